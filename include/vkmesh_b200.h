@@ -1,0 +1,157 @@
+/*
+ * vkmesh_b200 -- B200-native (CUDA sm_100a) implementation of everdoze/VulkanEngine's mesh-import
+ * geometry path, behind a C ABI.  No CPU fallback: every entry point fails with VKM_ERR_NO_DEVICE
+ * when there is no CUDA device.
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to the reference
+ * root).  INTEGRATION.md shows the engine-side binding.
+ */
+#ifndef VKMESH_B200_H
+#define VKMESH_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes (the reference signals failure with nullptr / false + a log line,
+ *      mesh_loader.cpp:55-58, 219-222; the shims in INTEGRATION.md map non-zero to that) ---- */
+#define VKM_OK 0
+#define VKM_ERR_INVALID_ARG 1 /* null pointer, corner count not a multiple of 3, sizes beyond 32-bit limits */
+#define VKM_ERR_BAD_INDEX 2   /* a v/vn/vt index is negative or out of range (undefined behaviour in the reference) */
+#define VKM_ERR_OOM 3         /* host or device allocation failed */
+#define VKM_ERR_CUDA 4        /* a CUDA call failed; see vkm_last_error() */
+#define VKM_ERR_NO_DEVICE 5   /* no CUDA device: there is no CPU path */
+#define VKM_ERR_CAPACITY 6    /* a plan's fixed capacity was exceeded */
+
+/* Engine::Vertex3D -- engine/src/renderer/renderer_types.hpp:13-19 (64 bytes, packed floats). */
+typedef struct vkm_vertex3d {
+    float position[3];
+    float normal[3];
+    float texcoord[2];
+    float color[4];
+    float tangent[4];
+} vkm_vertex3d;
+
+/* Engine::GeometryExtent -- engine/src/systems/resource/resources/mesh/mesh_resource.hpp:8-12. */
+typedef struct vkm_extent {
+    float center[3];
+    float min_extents[3];
+    float max_extents[3];
+} vkm_extent;
+
+/* The buffer part of Engine::GeometryConfig -- mesh_resource.hpp:14-24.  `vertices` and `indices` are
+ * malloc() memory, as the reference's are (Platform::AllocMemory, mesh_loader.cpp:303-304), so the
+ * engine's ~MeshResource / DisposeConfig can free() them (mesh_resource.cpp:13-18). */
+typedef struct vkm_shape_out {
+    uint32_t vertex_size;  /* 64 */
+    uint32_t vertex_count;
+    void* vertices;
+    uint32_t index_size;   /* 4 */
+    uint32_t index_count;
+    void* indices;
+    vkm_extent extent;
+} vkm_shape_out;
+
+/* ---- library state ---- */
+int vkm_device_count(void);
+/* Selects the CUDA devices the host entry points may use (default: device 0).  Optional. */
+int vkm_init(const int* device_ordinals, int count);
+void vkm_shutdown(void);
+/* Thread-local message of the last failing call on this thread. */
+const char* vkm_last_error(void);
+const char* vkm_version(void);
+
+/* ---- host entry points: drop-in for the reference's CPU functions (host pointers in, host pointers out) ---- */
+
+/* Replaces static void Geometry::GenerateTangents(u32 vertex_count, Vertex3D* vertices, u32 index_count,
+ * u32* indices) -- engine/src/resources/geometry/geometry.cpp:20-54 (declared geometry.hpp:49).
+ * In place: writes vertices[i].tangent for every vertex some triangle references; the triangle with the
+ * highest number wins, as in the reference's sequential loop. */
+int vkm_generate_tangents(uint32_t vertex_count, void* vertices, uint32_t index_count, const uint32_t* indices);
+
+/* Replaces static void Geometry::GenerateNormals(...) -- geometry.cpp:56-82 (geometry.hpp:50).  Flat face
+ * normals, last triangle wins. */
+int vkm_generate_normals(uint32_t vertex_count, void* vertices, uint32_t index_count, const uint32_t* indices);
+
+/* Replaces static u32 Geometry::DeduplicateVertices(u32 vertex_count, Vertex3D* vertices, u32 index_count,
+ * u32* indices, Vertex3D** out_vertices) -- geometry.cpp:94-126 (geometry.hpp:51).  Rewrites `indices` in
+ * place, returns the unique count and a malloc()ed *out_vertices.  Returns UINT32_MAX on failure. */
+uint32_t vkm_deduplicate_vertices(uint32_t vertex_count, const void* vertices, uint32_t index_count,
+                                  uint32_t* indices, void** out_vertices);
+
+/* Replaces the per-shape loop of MeshResource* MeshLoader::LoadOBJ(const std::string&, const std::string&)
+ * -- engine/src/systems/resource/loaders/mesh/mesh_loader.cpp:228-325: face expansion, first-occurrence
+ * vertex dedup, bounding box and tangent generation for every shape tinyobj produced.
+ *   pos / nrm / uv  : tinyobj::attrib_t::vertices / normals / texcoords (tinyobj.hpp:387-398)
+ *   idx_vnt         : concatenated tinyobj::index_t streams, 3 ints per corner in (vertex, normal, texcoord)
+ *                     order (tinyobj.hpp:347-351)
+ *   shape_corner_offsets : nshapes + 1 offsets into idx_vnt, in corners (each a multiple of 3)
+ *   out             : nshapes entries, filled with malloc()ed buffers; release with vkm_free_shape(). */
+int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t nn, const float* uv, uint64_t nt,
+                      const int32_t* idx_vnt, const uint64_t* shape_corner_offsets, uint32_t nshapes,
+                      vkm_shape_out* out);
+void vkm_free_shape(vkm_shape_out* shape);
+
+/* Pinned host memory for callers that want full-speed PCIe transfers through the host entry points. */
+void* vkm_host_alloc(uint64_t bytes);
+void vkm_host_free(void* p);
+
+/* ---- device-resident entry points (inputs and outputs stay in HBM; used by bench.py and by a renderer
+ *      that consumes the buffers on the GPU).  They replace the same reference loop as vkm_import_shapes;
+ *      the reference has no device-resident counterpart (its only device boundary is the Vulkan staging
+ *      copy, engine/src/renderer/backend/vulkan/vulkan.cpp:15-27). ---- */
+typedef struct vkm_plan vkm_plan;
+
+typedef struct vkm_plan_desc {
+    int device;                /* CUDA ordinal */
+    uint64_t max_corners;      /* capacity: corners per import (3 x triangles) */
+    uint64_t max_vertices;     /* capacity: unique vertices per import; 0 = worst case (= max_corners) */
+    uint64_t max_attrib;       /* largest of Np, Nn, Nt (sizes the hash tables; 0 = derive from max_corners) */
+    uint32_t max_shapes;
+} vkm_plan_desc;
+
+/* Per-import summary, valid after vkm_plan_finish(). */
+typedef struct vkm_plan_result {
+    uint64_t total_vertices;       /* sum over shapes */
+    uint64_t total_indices;
+    const void* d_vertices;        /* device: total_vertices x 64 B, shapes back to back */
+    const uint32_t* d_indices;     /* device: total_indices x u32, per-shape local indices */
+    const uint32_t* shape_vertex_offsets; /* host, nshapes + 1 */
+    const vkm_extent* shape_extents;      /* host, nshapes */
+    float phase_ms[8];             /* device time per pipeline phase when timing was requested, else 0 */
+} vkm_plan_result;
+
+int vkm_plan_create(const vkm_plan_desc* desc, vkm_plan** out);
+void vkm_plan_destroy(vkm_plan* plan);
+/* Enqueues the whole import on `stream` (a cudaStream_t; NULL = the plan's own stream).  All pointers are
+ * device pointers except shape_corner_offsets (host).  Asynchronous. */
+int vkm_plan_import(vkm_plan* plan, const float* d_pos, uint64_t np, const float* d_nrm, uint64_t nn,
+                    const float* d_uv, uint64_t nt, const int32_t* d_idx_vnt, const uint64_t* shape_corner_offsets,
+                    uint32_t nshapes, void* stream);
+/* Waits for the import, checks the device status word and fills `result`. */
+int vkm_plan_finish(vkm_plan* plan, vkm_plan_result* result);
+/* When enabled, vkm_plan_import records CUDA events between phases (costs a few microseconds). */
+void vkm_plan_set_timing(vkm_plan* plan, int enabled);
+/* Names of the phases reported in vkm_plan_result.phase_ms (NULL past the last). */
+const char* vkm_plan_phase_name(int phase);
+
+/* Device-resident Geometry::GenerateTangents / GenerateNormals (geometry.cpp:20-82) on caller-owned device
+ * buffers; `d_scratch` must hold vertex_count u32 (it is overwritten). */
+int vkm_generate_tangents_dev(uint32_t vertex_count, void* d_vertices, uint32_t index_count,
+                              const uint32_t* d_indices, uint32_t* d_scratch, void* stream);
+int vkm_generate_normals_dev(uint32_t vertex_count, void* d_vertices, uint32_t index_count,
+                             const uint32_t* d_indices, uint32_t* d_scratch, void* stream);
+
+/* Thin device-memory helpers so that non-CUDA callers (ctypes, the bench) need no second runtime. */
+int vkm_dev_alloc(int device, uint64_t bytes, void** d_ptr);
+int vkm_dev_free(int device, void* d_ptr);
+int vkm_dev_upload(int device, void* d_dst, const void* h_src, uint64_t bytes);
+int vkm_dev_download(int device, void* h_dst, const void* d_src, uint64_t bytes);
+int vkm_dev_sync(int device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VKMESH_B200_H */

@@ -1,0 +1,217 @@
+"""GPU parity tests (pytest -m gpu, on the B200 box): the CUDA path, called through the C ABI, against
+the oracle (oracle/oracle_port.c, pinned by tests/test_oracle.py) and the committed golden fixtures.
+
+Bars: index buffers bit-exact; vertex position/normal/uv/color bit-exact; tangents bit-exact (the
+kernels use round-to-nearest intrinsics without FMA contraction), NaN matches NaN regardless of
+sign/payload; extents equal by value.
+"""
+import numpy as np
+import pytest
+from conftest import assert_shapes_equal, load_golden, vertices_equal
+
+from oracle import port
+from oracle.refcpu import VERTEX_DTYPE, ShapeResult
+from vulkanengine_b200 import capi, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def golden_shapes(g):
+    return [ShapeResult(np.ascontiguousarray(g[f"vertices{i}"]).view(VERTEX_DTYPE).reshape(-1), g[f"indices{i}"],
+                        g[f"extent{i}"]) for i in range(int(g["nshapes"]))]
+
+
+def oracle_of(m):
+    return port.import_arrays(m.pos, m.nrm, m.uv, m.idx, m.shape_offsets)
+
+
+def gpu_of(m):
+    return capi.import_shapes(m.pos, m.nrm, m.uv, m.idx, m.shape_offsets)
+
+
+# ---------------------------------------------------------------- config 1: bundled assets (golden)
+@pytest.mark.parametrize("name", ["falcon", "viking_room", "semantics"])
+def test_import_matches_reference_golden(name):
+    g = load_golden(name)
+    got = capi.import_shapes(g["pos"], g["nrm"], g["uv"], g["idx"], g["shape_offsets"])
+    assert_shapes_equal(got, golden_shapes(g))
+
+
+def test_cube_normals_then_tangents_golden():
+    g = load_golden("cube")
+    v = np.ascontiguousarray(g["vertices_in"]).view(capi.VERTEX_DTYPE).reshape(-1).copy()
+    capi.generate_normals(v, g["indices"])
+    capi.generate_tangents(v, g["indices"])
+    ok, msg = vertices_equal(v, g["vertices_out"])
+    assert ok, msg
+
+
+# ---------------------------------------------------------------- synthetic meshes vs the oracle
+@pytest.mark.parametrize("mesh", [
+    lambda: synth.grid(1), lambda: synth.grid(2), lambda: synth.grid(37), lambda: synth.grid(200),
+    lambda: synth.grid(96, permute_seed=11), lambda: synth.uv_sphere(16, 32), lambda: synth.uv_sphere(64, 1024),
+    lambda: synth.adversarial(48), lambda: synth.adversarial(300, frac=5e-3, nan_frac=2e-3),
+], ids=["grid1", "grid2", "grid37", "grid200", "grid96perm", "sphere16", "sphere_pole1024", "adv48", "adv300"])
+def test_import_matches_oracle(mesh):
+    m = mesh()
+    assert_shapes_equal(gpu_of(m), oracle_of(m))
+
+
+def test_config2_grid_1m_matches_oracle():
+    m = synth.grid(708)  # 1 002 528 triangles
+    got, want = gpu_of(m), oracle_of(m)
+    assert len(want[0].vertices) == 709 * 709
+    assert_shapes_equal(got, want)
+
+
+def test_multi_shape_batch_matches_oracle():
+    meshes = synth.batch(40, min_tris=20, max_tris=5000)
+    m = synth.concat(meshes)
+    assert_shapes_equal(gpu_of(m), oracle_of(m))
+
+
+def test_shapes_sharing_attribute_arrays_dedup_per_shape():
+    # one OBJ with two `o` groups that reference the same v/vt/vn records: indices restart per shape
+    g = synth.grid(10)
+    idx = np.concatenate([g.idx, g.idx[::-1].reshape(-1, 3, 3)[:, ::-1].reshape(-1, 3)])
+    so = np.array([0, len(g.idx), 2 * len(g.idx)], np.uint64)
+    got = capi.import_shapes(g.pos, g.nrm, g.uv, idx, so)
+    want = port.import_arrays(g.pos, g.nrm, g.uv, idx, so)
+    assert_shapes_equal(got, want)
+    assert got[1].indices[0] == 0
+
+
+def test_empty_and_ragged_inputs():
+    g = synth.grid(3)
+    # empty shape between two real ones, and an empty trailing shape
+    so = np.array([0, 9, 9, len(g.idx), len(g.idx)], np.uint64)
+    got = capi.import_shapes(g.pos, g.nrm, g.uv, g.idx, so)
+    want = port.import_arrays(g.pos, g.nrm, g.uv, g.idx, so)
+    assert_shapes_equal(got, want)
+    assert got[1].vertices.size == 0 and got[1].indices.size == 0 and not got[1].extent.any()
+    # nothing at all
+    out = capi.import_shapes(g.pos, g.nrm, g.uv, np.empty((0, 3), np.int32), np.array([0, 0], np.uint64))
+    assert out[0].vertices.size == 0 and out[0].indices.size == 0
+
+
+def test_error_behaviour():
+    g = synth.grid(3)
+    bad = g.idx.copy()
+    bad[5, 2] = -1  # tinyobj's "absent" marker: undefined behaviour in the reference, an error here
+    with pytest.raises(capi.VkmError) as e:
+        capi.import_shapes(g.pos, g.nrm, g.uv, bad, g.shape_offsets)
+    assert e.value.code == 2
+    bad = g.idx.copy()
+    bad[7, 0] = len(g.pos)
+    with pytest.raises(capi.VkmError) as e:
+        capi.import_shapes(g.pos, g.nrm, g.uv, bad, g.shape_offsets)
+    assert e.value.code == 2
+    with pytest.raises(capi.VkmError) as e:  # not whole triangles
+        capi.import_shapes(g.pos, g.nrm, g.uv, g.idx[:10], np.array([0, 10], np.uint64))
+    assert e.value.code == 1
+    # the library still works afterwards
+    assert_shapes_equal(gpu_of(g), oracle_of(g))
+
+
+def test_all_unique_corners_grows_tables():
+    # no sharing at all: distinct triplets == corners, far above the optimistic table size
+    rng = np.random.default_rng(5)
+    n = 30000
+    pos = rng.standard_normal((64, 3)).astype(np.float32)
+    nrm = rng.standard_normal((64, 3)).astype(np.float32)
+    uv = rng.random((n, 2)).astype(np.float32)
+    idx = np.stack([rng.integers(0, 64, n), rng.integers(0, 64, n), np.arange(n)], 1).astype(np.int32)
+    so = np.array([0, n], np.uint64)
+    assert_shapes_equal(capi.import_shapes(pos, nrm, uv, idx, so), port.import_arrays(pos, nrm, uv, idx, so))
+
+
+def test_value_duplicates_with_distinct_triplets_merge():
+    # every attribute record exists twice: 8 different triplets per vertex value
+    g = synth.grid(20)
+    u = len(g.pos)
+    pos, nrm, uv = np.tile(g.pos, (2, 1)), np.tile(g.nrm, (2, 1)), np.tile(g.uv, (2, 1))
+    rng = np.random.default_rng(9)
+    idx = g.idx + (rng.integers(0, 2, g.idx.shape) * u).astype(np.int32)
+    got = capi.import_shapes(pos, nrm, uv, idx, g.shape_offsets)
+    want = port.import_arrays(pos, nrm, uv, idx, g.shape_offsets)
+    assert len(want[0].vertices) == u
+    assert_shapes_equal(got, want)
+
+
+# ---------------------------------------------------------------- stand-alone utilities
+@pytest.mark.parametrize("mesh", [lambda: synth.grid(50), lambda: synth.uv_sphere(20, 40), lambda: synth.adversarial(40)])
+def test_generate_tangents_and_normals_match_oracle(mesh):
+    m = mesh()
+    base = oracle_of(m)[0]
+    rng = np.random.default_rng(3)
+    for fn_gpu, fn_cpu in [(capi.generate_tangents, port.generate_tangents), (capi.generate_normals, port.generate_normals)]:
+        a = base.vertices.copy()
+        # poison the outputs so that untouched (unreferenced) vertices must stay untouched
+        a["tangent"] = rng.standard_normal(a["tangent"].shape).astype(np.float32)
+        b = a.copy()
+        fn_gpu(a.view(capi.VERTEX_DTYPE), base.indices)
+        fn_cpu(b, base.indices)
+        ok, msg = vertices_equal(a, b)
+        assert ok, msg
+
+
+def test_generate_tangents_out_of_range_index_is_an_error():
+    v = np.zeros(3, capi.VERTEX_DTYPE)
+    with pytest.raises(capi.VkmError) as e:
+        capi.generate_tangents(v, np.array([0, 1, 3], np.uint32))
+    assert e.value.code == 2
+
+
+# ---------------------------------------------------------------- device-resident plan API
+def test_plan_device_resident_matches_host_entry():
+    m = synth.concat([synth.grid(64), synth.uv_sphere(12, 24), synth.adversarial(32)])
+    dev = 0
+    d = [capi.DeviceArray(dev, a) for a in (m.pos, m.nrm, m.uv, m.idx)]
+    plan = capi.Plan(dev, m.corners, max_attrib=max(len(m.pos), len(m.nrm), len(m.uv)), max_shapes=3)
+    plan.set_timing(True)
+    for _ in range(2):  # plans are reusable
+        plan.import_async(d[0].ptr, len(m.pos), d[1].ptr, len(m.nrm), d[2].ptr, len(m.uv), d[3].ptr, m.shape_offsets)
+        r = plan.finish()
+        got = plan.fetch(r, m.shape_offsets)
+        assert_shapes_equal(got, oracle_of(m))
+    assert sum(r.phase_ms) > 0
+    with pytest.raises(capi.VkmError) as e:  # capacity is fixed at creation
+        plan.import_async(d[0].ptr, len(m.pos), d[1].ptr, len(m.nrm), d[2].ptr, len(m.uv), d[3].ptr,
+                          np.array([0, m.corners + 3], np.uint64))
+    assert e.value.code == 6
+    plan.destroy()
+
+
+# ---------------------------------------------------------------- full-size property checks (no oracle run)
+def test_config3_16m_properties():
+    """16.7M-triangle high-duplication grid: too slow for the CPU oracle inside the test budget, so check
+    size-independent properties: first-occurrence order, round trip through the index buffer, known
+    unique count, and a sample of tangents against the oracle's arithmetic."""
+    n = 2896
+    m = synth.grid(n)
+    out = gpu_of(m)[0]
+    u = (n + 1) ** 2
+    assert len(out.vertices) == u and len(out.indices) == m.corners
+    idx = out.indices
+    # first-occurrence numbering: a new index is always previous max + 1
+    running = np.maximum.accumulate(idx)
+    assert idx[0] == 0 and np.all(np.diff(running.astype(np.int64)) <= 1) and running[-1] == u - 1
+    # expand -> dedup round trip: vertex[index[c]] is exactly the expanded corner c
+    c = np.random.default_rng(1).integers(0, m.corners, 200000)
+    v = out.vertices[idx[c]]
+    assert np.array_equal(v["position"].view(np.uint32), m.pos[m.idx[c, 0]].view(np.uint32))
+    assert np.array_equal(v["normal"].view(np.uint32), m.nrm[m.idx[c, 1]].view(np.uint32))
+    assert np.array_equal(v["texcoord"].view(np.uint32), m.uv[m.idx[c, 2]].view(np.uint32))
+    assert not out.vertices["color"].any()
+    # tangents: recompute a slice of the mesh with the oracle's GenerateTangents (last triangle wins needs
+    # all triangles that touch the sampled vertices: use the first rows, whose vertices are complete)
+    rows = 3
+    ntri = 2 * n * rows
+    sub_idx = idx[: 3 * ntri]
+    nv = int(sub_idx.max()) + 1
+    sub = out.vertices[:nv].copy()
+    sub["tangent"] = 0
+    port.generate_tangents(sub, sub_idx.copy())
+    complete = (n + 1) * (rows - 1)  # vertices whose every incident triangle lies in the slice
+    ok, msg = vertices_equal(sub[:complete], out.vertices[:complete])
+    assert ok, msg

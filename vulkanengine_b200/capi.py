@@ -1,0 +1,291 @@
+"""ctypes bindings for the C ABI of libvkmesh_b200.so (include/vkmesh_b200.h).
+
+These are what tests/ and bench.py call; the names mirror the reference's own interface for the path
+(MeshLoader::LoadOBJ's per-shape loop, Geometry::GenerateTangents / GenerateNormals /
+DeduplicateVertices).  There is no fallback: if the shared library is missing or there is no CUDA
+device the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import build as _build
+
+VERTEX_DTYPE = np.dtype(
+    [("position", "<f4", 3), ("normal", "<f4", 3), ("texcoord", "<f4", 2), ("color", "<f4", 4), ("tangent", "<f4", 4)]
+)
+
+VKM_OK = 0
+ERR_NAMES = {1: "INVALID_ARG", 2: "BAD_INDEX", 3: "OOM", 4: "CUDA", 5: "NO_DEVICE", 6: "CAPACITY"}
+
+# every symbol include/vkmesh_b200.h declares (tests check that the library exports all of them)
+SYMBOLS = [
+    "vkm_device_count", "vkm_init", "vkm_shutdown", "vkm_last_error", "vkm_version",
+    "vkm_generate_tangents", "vkm_generate_normals", "vkm_deduplicate_vertices",
+    "vkm_import_shapes", "vkm_free_shape", "vkm_host_alloc", "vkm_host_free",
+    "vkm_plan_create", "vkm_plan_destroy", "vkm_plan_import", "vkm_plan_finish", "vkm_plan_set_timing",
+    "vkm_plan_phase_name", "vkm_generate_tangents_dev", "vkm_generate_normals_dev",
+    "vkm_dev_alloc", "vkm_dev_free", "vkm_dev_upload", "vkm_dev_download", "vkm_dev_sync",
+]
+
+
+class VkmError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"vkmesh_b200 error {code} ({ERR_NAMES.get(code, '?')}): {msg}")
+        self.code = code
+
+
+class Extent(C.Structure):
+    _fields_ = [("center", C.c_float * 3), ("min_extents", C.c_float * 3), ("max_extents", C.c_float * 3)]
+
+
+class ShapeOut(C.Structure):
+    _fields_ = [("vertex_size", C.c_uint32), ("vertex_count", C.c_uint32), ("vertices", C.c_void_p),
+                ("index_size", C.c_uint32), ("index_count", C.c_uint32), ("indices", C.c_void_p),
+                ("extent", Extent)]
+
+
+class PlanDesc(C.Structure):
+    _fields_ = [("device", C.c_int), ("max_corners", C.c_uint64), ("max_vertices", C.c_uint64),
+                ("max_attrib", C.c_uint64), ("max_shapes", C.c_uint32)]
+
+
+class PlanResult(C.Structure):
+    _fields_ = [("total_vertices", C.c_uint64), ("total_indices", C.c_uint64), ("d_vertices", C.c_void_p),
+                ("d_indices", C.c_void_p), ("shape_vertex_offsets", C.POINTER(C.c_uint32)),
+                ("shape_extents", C.POINTER(Extent)), ("phase_ms", C.c_float * 8)]
+
+
+_lib = None
+
+
+def lib_path() -> str:
+    return _build.LIB_PATH
+
+
+def lib():
+    """Loads the shared library (building it first if the sources are newer).  Raises if that fails."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB_PATH
+    if not os.path.exists(path):
+        path = _build.build()
+    L = C.CDLL(path)
+    L.vkm_last_error.restype = C.c_char_p
+    L.vkm_version.restype = C.c_char_p
+    L.vkm_device_count.restype = C.c_int
+    L.vkm_init.argtypes = [C.POINTER(C.c_int), C.c_int]
+    for fn in (L.vkm_generate_tangents, L.vkm_generate_normals):
+        fn.restype = C.c_int
+        fn.argtypes = [C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p]
+    L.vkm_deduplicate_vertices.restype = C.c_uint32
+    L.vkm_deduplicate_vertices.argtypes = [C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_void_p)]
+    L.vkm_import_shapes.restype = C.c_int
+    L.vkm_import_shapes.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p,
+                                    C.c_void_p, C.c_uint32, C.POINTER(ShapeOut)]
+    L.vkm_free_shape.argtypes = [C.POINTER(ShapeOut)]
+    L.vkm_host_alloc.restype = C.c_void_p
+    L.vkm_host_alloc.argtypes = [C.c_uint64]
+    L.vkm_host_free.argtypes = [C.c_void_p]
+    L.vkm_plan_create.restype = C.c_int
+    L.vkm_plan_create.argtypes = [C.POINTER(PlanDesc), C.POINTER(C.c_void_p)]
+    L.vkm_plan_destroy.argtypes = [C.c_void_p]
+    L.vkm_plan_import.restype = C.c_int
+    L.vkm_plan_import.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                  C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
+    L.vkm_plan_finish.restype = C.c_int
+    L.vkm_plan_finish.argtypes = [C.c_void_p, C.POINTER(PlanResult)]
+    L.vkm_plan_set_timing.argtypes = [C.c_void_p, C.c_int]
+    L.vkm_plan_phase_name.restype = C.c_char_p
+    L.vkm_plan_phase_name.argtypes = [C.c_int]
+    for fn in (L.vkm_generate_tangents_dev, L.vkm_generate_normals_dev):
+        fn.restype = C.c_int
+        fn.argtypes = [C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.vkm_dev_alloc.restype = C.c_int
+    L.vkm_dev_alloc.argtypes = [C.c_int, C.c_uint64, C.POINTER(C.c_void_p)]
+    L.vkm_dev_free.argtypes = [C.c_int, C.c_void_p]
+    L.vkm_dev_upload.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint64]
+    L.vkm_dev_download.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint64]
+    L.vkm_dev_sync.argtypes = [C.c_int]
+    _lib = L
+    return L
+
+
+def _check(rc: int) -> None:
+    if rc != VKM_OK:
+        raise VkmError(rc, lib().vkm_last_error().decode())
+
+
+@dataclass
+class ShapeResult:
+    vertices: np.ndarray  # VERTEX_DTYPE [U]
+    indices: np.ndarray  # uint32 [C]
+    extent: np.ndarray  # float32 [9]: center, min_extents, max_extents
+
+
+def _copy_out(ptr, nbytes, dtype):
+    if not nbytes:
+        return np.empty(0, dtype)
+    return np.frombuffer((C.c_char * nbytes).from_address(ptr), dtype=dtype).copy()
+
+
+def init(devices=None) -> None:
+    if devices is None:
+        _check(lib().vkm_init(None, 0))
+    else:
+        arr = (C.c_int * len(devices))(*devices)
+        _check(lib().vkm_init(arr, len(devices)))
+
+
+def import_shapes(pos, nrm, uv, idx, shape_offsets) -> list:
+    """vkm_import_shapes: host arrays in, list of ShapeResult out (the per-shape loop of LoadOBJ)."""
+    L = lib()
+    pos = np.ascontiguousarray(pos, np.float32)
+    nrm = np.ascontiguousarray(nrm, np.float32)
+    uv = np.ascontiguousarray(uv, np.float32)
+    idx = np.ascontiguousarray(idx, np.int32)
+    so = np.ascontiguousarray(shape_offsets, np.uint64)
+    ns = len(so) - 1
+    out = (ShapeOut * max(ns, 1))()
+    _check(L.vkm_import_shapes(pos.ctypes.data, pos.size // 3, nrm.ctypes.data, nrm.size // 3, uv.ctypes.data,
+                               uv.size // 2, idx.ctypes.data, so.ctypes.data, ns, out))
+    res = []
+    for i in range(ns):
+        o = out[i]
+        assert o.vertex_size == 64 and o.index_size == 4
+        v = _copy_out(o.vertices, 64 * o.vertex_count, VERTEX_DTYPE)
+        ix = _copy_out(o.indices, 4 * o.index_count, np.uint32)
+        e = np.array(list(o.extent.center) + list(o.extent.min_extents) + list(o.extent.max_extents), np.float32)
+        res.append(ShapeResult(v, ix, e))
+        L.vkm_free_shape(C.byref(o))
+    return res
+
+
+def generate_tangents(vertices: np.ndarray, indices: np.ndarray) -> None:
+    assert vertices.dtype == VERTEX_DTYPE and vertices.flags.c_contiguous
+    idx = np.ascontiguousarray(indices, np.uint32)
+    _check(lib().vkm_generate_tangents(len(vertices), vertices.ctypes.data, len(idx), idx.ctypes.data))
+
+
+def generate_normals(vertices: np.ndarray, indices: np.ndarray) -> None:
+    assert vertices.dtype == VERTEX_DTYPE and vertices.flags.c_contiguous
+    idx = np.ascontiguousarray(indices, np.uint32)
+    _check(lib().vkm_generate_normals(len(vertices), vertices.ctypes.data, len(idx), idx.ctypes.data))
+
+
+def deduplicate_vertices(vertices: np.ndarray, indices: np.ndarray):
+    assert vertices.dtype == VERTEX_DTYPE
+    idx = np.ascontiguousarray(indices, np.uint32).copy()
+    out = C.c_void_p()
+    n = lib().vkm_deduplicate_vertices(len(vertices), vertices.ctypes.data, len(idx), idx.ctypes.data, C.byref(out))
+    if n == 0xFFFFFFFF:
+        raise VkmError(-1, lib().vkm_last_error().decode())
+    v = _copy_out(out.value, 64 * n, VERTEX_DTYPE)
+    C.CDLL(None).free(out)
+    return v, idx
+
+
+class DeviceArray:
+    """A device allocation made through vkm_dev_alloc (no second CUDA runtime needed)."""
+
+    def __init__(self, device: int, host: np.ndarray | None = None, nbytes: int | None = None):
+        self.device = device
+        self.nbytes = int(host.nbytes if host is not None else nbytes)
+        p = C.c_void_p()
+        _check(lib().vkm_dev_alloc(device, self.nbytes, C.byref(p)))
+        self.ptr = p.value
+        if host is not None and host.nbytes:
+            h = np.ascontiguousarray(host)
+            _check(lib().vkm_dev_upload(device, self.ptr, h.ctypes.data, h.nbytes))
+
+    def download(self, dtype, count: int | None = None, offset_bytes: int = 0) -> np.ndarray:
+        dt = np.dtype(dtype)
+        n = (self.nbytes - offset_bytes) // dt.itemsize if count is None else count
+        out = np.empty(n, dt)
+        if n:
+            _check(lib().vkm_dev_download(self.device, out.ctypes.data, self.ptr + offset_bytes, n * dt.itemsize))
+        return out
+
+    def free(self):
+        if self.ptr:
+            lib().vkm_dev_free(self.device, self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def download(device: int, ptr: int, dtype, count: int) -> np.ndarray:
+    dt = np.dtype(dtype)
+    out = np.empty(count, dt)
+    if count:
+        _check(lib().vkm_dev_download(device, out.ctypes.data, ptr, count * dt.itemsize))
+    return out
+
+
+class Plan:
+    """vkm_plan: device-resident import with preallocated scratch and outputs."""
+
+    def __init__(self, device: int, max_corners: int, max_attrib: int = 0, max_vertices: int = 0, max_shapes: int = 1):
+        d = PlanDesc(device, max_corners, max_vertices, max_attrib, max_shapes)
+        h = C.c_void_p()
+        _check(lib().vkm_plan_create(C.byref(d), C.byref(h)))
+        self.h = h
+        self.device = device
+        self.nshapes = 0
+
+    def set_timing(self, on: bool) -> None:
+        lib().vkm_plan_set_timing(self.h, 1 if on else 0)
+
+    def import_async(self, d_pos, np_, d_nrm, nn, d_uv, nt, d_idx, shape_offsets: np.ndarray, stream: int = 0) -> None:
+        so = np.ascontiguousarray(shape_offsets, np.uint64)
+        self.nshapes = len(so) - 1
+        _check(lib().vkm_plan_import(self.h, d_pos, np_, d_nrm, nn, d_uv, nt, d_idx, so.ctypes.data, self.nshapes,
+                                     C.c_void_p(stream)))
+
+    def finish(self) -> PlanResult:
+        r = PlanResult()
+        _check(lib().vkm_plan_finish(self.h, C.byref(r)))
+        return r
+
+    def fetch(self, r: PlanResult, shape_offsets: np.ndarray) -> list:
+        """Downloads the per-shape buffers of a finished import (test helper)."""
+        so = np.asarray(shape_offsets, np.uint64)
+        out = []
+        for s in range(self.nshapes):
+            v0, v1 = r.shape_vertex_offsets[s], r.shape_vertex_offsets[s + 1]
+            c0, c1 = int(so[s]), int(so[s + 1])
+            v = download(self.device, r.d_vertices + 64 * v0, VERTEX_DTYPE, v1 - v0)
+            ix = download(self.device, r.d_indices + 4 * c0, np.uint32, c1 - c0)
+            e = r.shape_extents[s]
+            ext = np.array(list(e.center) + list(e.min_extents) + list(e.max_extents), np.float32)
+            out.append(ShapeResult(v, ix, ext))
+        return out
+
+    def phase_names(self):
+        names, i = [], 0
+        while True:
+            n = lib().vkm_plan_phase_name(i)
+            if not n:
+                return names
+            names.append(n.decode())
+            i += 1
+
+    def destroy(self):
+        if self.h:
+            lib().vkm_plan_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass

@@ -1,0 +1,138 @@
+// Device-side building blocks shared by the kernels of the mesh-import path.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace vkm {
+
+constexpr uint64_t kEmpty64 = ~0ull;          // empty hash slot
+constexpr uint32_t kUnmatchable = 0xFFFFFFFFu; // aux marker: key holds NaN/Inf and never matches anything
+constexpr int kMaxProbe = 2048;
+
+// Device status block, read back by the host after every import.
+struct Status {
+    uint32_t bad_index;          // some v/vn/vt index out of range
+    uint32_t overflow1;          // triplet table too small
+    uint32_t overflow2;          // value table too small
+    uint32_t has_unmatchable;    // at least one NaN/Inf key was seen
+    uint32_t capacity_exceeded;  // unique vertices > plan capacity
+    uint32_t total_vertices;
+    uint32_t pad[2];
+};
+
+// Everything a kernel of the import pipeline may touch.  Passed by value.
+struct ImportArgs {
+    // inputs (tinyobj streams, device resident)
+    const float* pos;
+    const float* nrm;
+    const float* uv;
+    const int32_t* idx;  // 3 ints per corner: v, n, t
+    uint32_t np, nn, nt;
+    uint32_t ncorners;
+    const uint32_t* shape_off;  // nshapes + 1 corner offsets
+    uint32_t nshapes;
+    // scratch
+    uint64_t* table1;  // triplet table: (tag << 32 | first corner)
+    uint32_t m1;
+    uint64_t* table2;  // value table:   (tag << 32 | first corner)
+    uint32_t m2;
+    uint32_t* slot1;   // [ncorners] slot of every corner in table1
+    uint32_t* aux1;    // [m1] per triplet: slot in table2, later the final local vertex index
+    uint32_t* fbits;   // [nwords + 1] bit c set <=> corner c creates a vertex
+    uint32_t* fprefix; // [nwords + 1] exclusive popcount prefix of fbits
+    uint32_t* block_sums;
+    uint32_t nwords;
+    uint32_t* ext_enc;  // [nshapes * 6] order-encoded min xyz, max xyz
+    uint32_t* vbase;    // [nshapes + 1] first global vertex id of every shape
+    uint32_t* lastface; // [vertex capacity] 1 + highest face id that references the vertex
+    // outputs
+    uint32_t* out_idx;  // [ncorners] per-shape local indices
+    float4* out_vtx;    // [vertex capacity * 4]
+    uint32_t vertex_capacity;
+    Status* status;
+};
+
+__device__ __forceinline__ uint64_t mix64(uint64_t x) {
+    x ^= x >> 33;
+    x *= 0xff51afd7ed558ccdull;
+    x ^= x >> 33;
+    x *= 0xc4ceb9fe1a85ec53ull;
+    x ^= x >> 33;
+    return x;
+}
+
+__device__ __forceinline__ uint64_t hash_triplet(uint32_t v, uint32_t n, uint32_t t, uint32_t shape) {
+    const uint64_t a = (uint64_t)v | ((uint64_t)n << 32);
+    const uint64_t b = (uint64_t)t | ((uint64_t)shape << 32);
+    return mix64(a ^ mix64(b + 0x9e3779b97f4a7c15ull));
+}
+
+__device__ __forceinline__ uint64_t hash_key8(const uint32_t k[8], uint32_t shape) {
+    uint64_t h = mix64(((uint64_t)k[0] | ((uint64_t)k[1] << 32)) + 0x9e3779b97f4a7c15ull * (shape + 1));
+    h = mix64(h ^ ((uint64_t)k[2] | ((uint64_t)k[3] << 32)));
+    h = mix64(h ^ ((uint64_t)k[4] | ((uint64_t)k[5] << 32)));
+    h = mix64(h ^ ((uint64_t)k[6] | ((uint64_t)k[7] << 32)));
+    return h;
+}
+
+// Range reduction without a power-of-two table: floor(x * m / 2^32).
+__device__ __forceinline__ uint32_t reduce32(uint32_t x, uint32_t m) { return __umulhi(x, m); }
+
+// Largest s with shape_off[s] <= c (empty shapes are skipped because the search is an upper bound).
+__device__ __forceinline__ uint32_t find_shape(const uint32_t* __restrict__ shape_off, uint32_t nshapes, uint32_t c) {
+    if (nshapes <= 1) return 0;
+    uint32_t lo = 0, hi = nshapes;  // invariant: shape_off[lo] <= c < shape_off[hi]
+    while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(shape_off + mid) <= c) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// Monotone float -> uint map (so that integer atomicMin/Max order floats).  Never fed NaN.
+__device__ __forceinline__ uint32_t enc_float(float f) {
+    const uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float dec_float(uint32_t e) {
+    const uint32_t b = (e & 0x80000000u) ? (e & 0x7FFFFFFFu) : ~e;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(b);
+#else
+    float f;
+    memcpy(&f, &b, 4);
+    return f;
+#endif
+}
+
+__device__ __forceinline__ bool nonfinite_bits(uint32_t b) { return (b & 0x7F800000u) == 0x7F800000u; }
+__device__ __forceinline__ uint32_t canon_bits(uint32_t b) { return b == 0x80000000u ? 0u : b; }
+
+// Global rank (number of vertex-creating corners before corner c).
+__device__ __forceinline__ uint32_t rank_of(const ImportArgs& a, uint32_t c) {
+    const uint32_t w = c >> 5;
+    return a.fprefix[w] + __popc(a.fbits[w] & ((1u << (c & 31)) - 1u));
+}
+
+// Loads the 8 live floats of a corner's expanded vertex (position, normal, texcoord) as raw bits.
+// Indices are clamped so that a flagged bad index can never fault.
+__device__ __forceinline__ void gather_key(const ImportArgs& a, uint32_t v, uint32_t n, uint32_t t, uint32_t k[8]) {
+    v = min(v, a.np - 1);
+    n = min(n, a.nn - 1);
+    t = min(t, a.nt - 1);
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(a.pos) + 3ull * v;
+    const uint32_t* q = reinterpret_cast<const uint32_t*>(a.nrm) + 3ull * n;
+    const uint32_t* r = reinterpret_cast<const uint32_t*>(a.uv) + 2ull * t;
+    k[0] = __ldg(p);
+    k[1] = __ldg(p + 1);
+    k[2] = __ldg(p + 2);
+    k[3] = __ldg(q);
+    k[4] = __ldg(q + 1);
+    k[5] = __ldg(q + 2);
+    const uint2 tt = __ldg(reinterpret_cast<const uint2*>(r));
+    k[6] = tt.x;
+    k[7] = tt.y;
+}
+
+}  // namespace vkm

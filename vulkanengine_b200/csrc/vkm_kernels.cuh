@@ -1,0 +1,491 @@
+// sm_100a kernels of the mesh-import path (all HBM/L2-bound integer + gather work; no tensor cores).
+//
+//   k_insert_triplets   A2/A3  read the (v,n,t) index stream with 128-bit loads, hash-insert every corner
+//                              into the triplet table with atomicMin(first corner)          [C-scale]
+//   k_resolve_firsts    A2/A3/A4  first corner of every distinct triplet: gather 8 floats, bounding box,
+//                              NaN/Inf screening, hash-insert the VALUE key into table2      [T-scale work]
+//   k_mark_unmatchable  A3     NaN/Inf keys: every occurrence creates a vertex (only runs if any seen)
+//   k_mark_value_firsts A3     table2 -> one flag bit per vertex-creating corner
+//   k_scan_*            A3     popcount prefix over the flag bitmap (stable first-occurrence order)
+//   k_shape_bases       A8     per-shape vertex base / count
+//   k_final_index       A3     per triplet: final local vertex index
+//   k_write_indices     A3/A5  per corner: index buffer + atomicMax(last face per vertex)   [C-scale]
+//   k_write_vertices    A2/A8  stable compaction: 64-byte Vertex3D records
+//   k_tangents/normals  A5/A6  per vertex: evaluate the winning (highest-numbered) triangle
+//
+// Row ids refer to SURVEY.md section 8(a).
+#pragma once
+
+#include "vkm_device.cuh"
+
+namespace vkm {
+
+constexpr int kThreads = 256;
+
+// ---------------------------------------------------------------------------------------------
+// K1: triplet insert.  Each thread owns 4 consecutive corners = 48 bytes = three 128-bit loads.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t insert_triplet(const ImportArgs& a, uint32_t c, uint32_t v, uint32_t n, uint32_t t,
+                                                   uint32_t sh, uint32_t sh_begin, uint32_t sh_end) {
+    const uint64_t h = hash_triplet(v, n, t, sh);
+    const uint32_t tag = (uint32_t)(h >> 32);
+    const uint64_t mine = ((uint64_t)tag << 32) | c;
+    uint32_t s = reduce32((uint32_t)h, a.m1);
+    for (int probe = 0; probe < kMaxProbe; ++probe) {
+        uint64_t cur = __ldcg(a.table1 + s);
+        if (cur == kEmpty64) {
+            const uint64_t prev = atomicCAS(reinterpret_cast<unsigned long long*>(a.table1 + s), kEmpty64, mine);
+            if (prev == kEmpty64) return s;
+            cur = prev;
+        }
+        if ((uint32_t)(cur >> 32) == tag) {
+            const uint32_t occ = (uint32_t)cur;
+            if (occ == c) return s;
+            // Exact check: a slot only ever holds corners of one (shape, v, n, t); tags merely skip gathers.
+            if (occ >= sh_begin && occ < sh_end) {
+                const int32_t* o = a.idx + 3ull * occ;
+                if ((uint32_t)__ldg(o) == v && (uint32_t)__ldg(o + 1) == n && (uint32_t)__ldg(o + 2) == t) {
+                    if (occ > c) atomicMin(reinterpret_cast<unsigned long long*>(a.table1 + s), mine);
+                    return s;
+                }
+            }
+        }
+        s = (s + 1 == a.m1) ? 0 : s + 1;
+    }
+    a.status->overflow1 = 1;
+    return 0;
+}
+
+__global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
+    const uint32_t ngroups = (a.ncorners + 3) >> 2;
+    for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
+        const uint32_t c0 = g << 2;
+        int32_t w[12];
+        if (c0 + 4 <= a.ncorners) {
+            const int4* src = reinterpret_cast<const int4*>(a.idx + 3ull * c0);
+            const int4 x = __ldg(src), y = __ldg(src + 1), z = __ldg(src + 2);
+            w[0] = x.x; w[1] = x.y; w[2] = x.z; w[3] = x.w;
+            w[4] = y.x; w[5] = y.y; w[6] = y.z; w[7] = y.w;
+            w[8] = z.x; w[9] = z.y; w[10] = z.z; w[11] = z.w;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 12; ++i) w[i] = (c0 + i / 3 < a.ncorners) ? __ldg(a.idx + 3ull * c0 + i) : 0;
+        }
+        uint32_t sh = find_shape(a.shape_off, a.nshapes, c0);
+        uint32_t sh_begin = a.shape_off[sh], sh_end = a.shape_off[sh + 1];
+        uint32_t slots[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t c = c0 + i;
+            slots[i] = 0;
+            if (c >= a.ncorners) continue;
+            if (c >= sh_end) {
+                sh = find_shape(a.shape_off, a.nshapes, c);
+                sh_begin = a.shape_off[sh];
+                sh_end = a.shape_off[sh + 1];
+            }
+            uint32_t v = (uint32_t)w[3 * i], n = (uint32_t)w[3 * i + 1], t = (uint32_t)w[3 * i + 2];
+            if (v >= a.np || n >= a.nn || t >= a.nt) {  // negative ints are huge as unsigned
+                a.status->bad_index = 1;
+                continue;
+            }
+            slots[i] = insert_triplet(a, c, v, n, t, sh, sh_begin, sh_end);
+        }
+        if (c0 + 4 <= a.ncorners) {
+            *reinterpret_cast<uint4*>(a.slot1 + c0) = make_uint4(slots[0], slots[1], slots[2], slots[3]);
+        } else {
+            for (int i = 0; i < 4 && c0 + i < a.ncorners; ++i) a.slot1[c0 + i] = slots[i];
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2: first corner of each distinct triplet -> bounding box, NaN/Inf screening, value-key insert.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool same_value_key(const ImportArgs& a, uint32_t occ, const uint32_t k[8]) {
+    const int32_t* o = a.idx + 3ull * occ;
+    uint32_t q[8];
+    gather_key(a, (uint32_t)__ldg(o), (uint32_t)__ldg(o + 1), (uint32_t)__ldg(o + 2), q);
+    bool eq = true;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) eq &= (canon_bits(q[i]) == k[i]);
+    return eq;
+}
+
+__device__ __forceinline__ uint32_t insert_value(const ImportArgs& a, uint32_t c, const uint32_t k[8], uint32_t sh,
+                                                 uint32_t sh_begin, uint32_t sh_end) {
+    const uint64_t h = hash_key8(k, sh);
+    const uint32_t tag = (uint32_t)(h >> 32);
+    const uint64_t mine = ((uint64_t)tag << 32) | c;
+    uint32_t s = reduce32((uint32_t)h, a.m2);
+    for (int probe = 0; probe < kMaxProbe; ++probe) {
+        uint64_t cur = __ldcg(a.table2 + s);
+        if (cur == kEmpty64) {
+            const uint64_t prev = atomicCAS(reinterpret_cast<unsigned long long*>(a.table2 + s), kEmpty64, mine);
+            if (prev == kEmpty64) return s;
+            cur = prev;
+        }
+        if ((uint32_t)(cur >> 32) == tag) {
+            const uint32_t occ = (uint32_t)cur;
+            if (occ == c) return s;
+            if (occ >= sh_begin && occ < sh_end && same_value_key(a, occ, k)) {
+                if (occ > c) atomicMin(reinterpret_cast<unsigned long long*>(a.table2 + s), mine);
+                return s;
+            }
+        }
+        s = (s + 1 == a.m2) ? 0 : s + 1;
+    }
+    a.status->overflow2 = 1;
+    return 0;
+}
+
+__global__ void __launch_bounds__(kThreads) k_resolve_firsts(ImportArgs a) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t padded = (a.ncorners + 31) & ~31u;  // whole warps stay in the loop (warp reductions below)
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < padded; c += gridDim.x * blockDim.x) {
+        const uint32_t neutral = 0x80000000u;  // enc_float(+0): the reference's box always contains the origin
+        uint32_t mn0 = neutral, mn1 = neutral, mn2 = neutral, mx0 = neutral, mx1 = neutral, mx2 = neutral;
+        uint32_t sh = 0;
+        bool first = false;
+        if (c < a.ncorners) {
+            const uint32_t s = a.slot1[c];
+            first = ((uint32_t)__ldcg(a.table1 + s) == c);
+            sh = find_shape(a.shape_off, a.nshapes, c);
+        }
+        if (first) {
+            const int32_t* o = a.idx + 3ull * c;
+            uint32_t k[8];
+            gather_key(a, (uint32_t)__ldg(o), (uint32_t)__ldg(o + 1), (uint32_t)__ldg(o + 2), k);
+            bool bad = false;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) bad |= nonfinite_bits(k[i]);
+            // strict </> against NaN never updates the reference's box; +-Inf does
+            if ((k[0] & 0x7FFFFFFFu) <= 0x7F800000u) mn0 = mx0 = enc_float(__uint_as_float(k[0]));
+            if ((k[1] & 0x7FFFFFFFu) <= 0x7F800000u) mn1 = mx1 = enc_float(__uint_as_float(k[1]));
+            if ((k[2] & 0x7FFFFFFFu) <= 0x7F800000u) mn2 = mx2 = enc_float(__uint_as_float(k[2]));
+            const uint32_t s1 = a.slot1[c];
+            if (bad) {
+                a.aux1[s1] = kUnmatchable;
+                a.status->has_unmatchable = 1;
+                atomicOr(a.fbits + (c >> 5), 1u << (c & 31));
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) k[i] = canon_bits(k[i]);
+                a.aux1[s1] = insert_value(a, c, k, sh, a.shape_off[sh], a.shape_off[sh + 1]);
+            }
+        }
+        // bounding box: warp-reduce when the warp sits inside one shape, else per-thread atomics
+        const uint32_t sh0 = __shfl_sync(0xFFFFFFFFu, sh, 0);
+        const bool uniform = __all_sync(0xFFFFFFFFu, sh == sh0 || c >= a.ncorners);
+        if (uniform) {
+            mn0 = __reduce_min_sync(0xFFFFFFFFu, mn0);
+            mn1 = __reduce_min_sync(0xFFFFFFFFu, mn1);
+            mn2 = __reduce_min_sync(0xFFFFFFFFu, mn2);
+            mx0 = __reduce_max_sync(0xFFFFFFFFu, mx0);
+            mx1 = __reduce_max_sync(0xFFFFFFFFu, mx1);
+            mx2 = __reduce_max_sync(0xFFFFFFFFu, mx2);
+        }
+        if ((uniform && lane == 0) || (!uniform && first)) {
+            uint32_t* e = a.ext_enc + 6u * (uniform ? sh0 : sh);
+            // bounds converge quickly: read (possibly stale, monotone) values first, atomics only on improvement
+            if (mn0 < e[0]) atomicMin(e + 0, mn0);
+            if (mn1 < e[1]) atomicMin(e + 1, mn1);
+            if (mn2 < e[2]) atomicMin(e + 2, mn2);
+            if (mx0 > e[3]) atomicMax(e + 3, mx0);
+            if (mx1 > e[4]) atomicMax(e + 4, mx1);
+            if (mx2 > e[5]) atomicMax(e + 5, mx2);
+        }
+    }
+}
+
+// Every occurrence of a NaN/Inf key creates a vertex (and gets index 0); firsts were flagged in K2.
+__global__ void __launch_bounds__(kThreads) k_mark_unmatchable(ImportArgs a) {
+    if (a.status->has_unmatchable == 0) return;
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < a.ncorners; c += gridDim.x * blockDim.x) {
+        if (a.aux1[a.slot1[c]] == kUnmatchable) atomicOr(a.fbits + (c >> 5), 1u << (c & 31));
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_mark_value_firsts(ImportArgs a) {
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < a.m2; s += gridDim.x * blockDim.x) {
+        const uint64_t cur = a.table2[s];
+        if (cur != kEmpty64) {
+            const uint32_t c = (uint32_t)cur;
+            atomicOr(a.fbits + (c >> 5), 1u << (c & 31));
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Popcount prefix over the flag bitmap: three small kernels (the bitmap is C/8 bytes).
+// ---------------------------------------------------------------------------------------------
+constexpr int kScanThreads = 1024;
+constexpr int kScanItems = 4;  // words per thread
+constexpr int kScanTile = kScanThreads * kScanItems;
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t x, uint32_t* total) {
+    __shared__ uint32_t warp_sums[32];
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t inc = x;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if (lane >= d) inc += y;
+    }
+    if (lane == 31) warp_sums[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t ws = (lane < (blockDim.x >> 5)) ? warp_sums[lane] : 0;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, ws, d);
+            if (lane >= d) ws += y;
+        }
+        warp_sums[lane] = ws;
+    }
+    __syncthreads();
+    const uint32_t base = wid ? warp_sums[wid - 1] : 0;
+    if (total) *total = warp_sums[(blockDim.x >> 5) - 1];
+    __syncthreads();
+    return base + inc - x;
+}
+
+__global__ void __launch_bounds__(kScanThreads) k_scan_tiles(ImportArgs a) {
+    const uint32_t base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i)
+        if (base + i < a.nwords) sum += __popc(a.fbits[base + i]);
+    uint32_t total;
+    block_exclusive_scan(sum, &total);
+    if (threadIdx.x == 0) a.block_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(kScanThreads) k_scan_block_sums(ImportArgs a, uint32_t nblocks) {
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t b0 = 0; b0 < nblocks; b0 += kScanThreads) {
+        const uint32_t i = b0 + threadIdx.x;
+        const uint32_t x = (i < nblocks) ? a.block_sums[i] : 0;
+        uint32_t total;
+        const uint32_t ex = block_exclusive_scan(x, &total);
+        const uint32_t c = carry;
+        if (i < nblocks) a.block_sums[i] = c + ex;
+        __syncthreads();
+        if (threadIdx.x == 0) carry = c + total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        a.fprefix[a.nwords] = carry;  // rank(ncorners) when ncorners % 32 == 0
+        a.status->total_vertices = carry;
+        if (carry > a.vertex_capacity) a.status->capacity_exceeded = 1;
+    }
+}
+
+__global__ void __launch_bounds__(kScanThreads) k_scan_write(ImportArgs a) {
+    const uint32_t base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    uint32_t pc[kScanItems];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+        pc[i] = (base + i < a.nwords) ? __popc(a.fbits[base + i]) : 0;
+        sum += pc[i];
+    }
+    uint32_t run = a.block_sums[blockIdx.x] + block_exclusive_scan(sum, nullptr);
+#pragma unroll
+    for (int i = 0; i < kScanItems; ++i) {
+        if (base + i < a.nwords) a.fprefix[base + i] = run;
+        run += pc[i];
+    }
+}
+
+__global__ void k_shape_bases(ImportArgs a) {
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s <= a.nshapes; s += gridDim.x * blockDim.x)
+        a.vbase[s] = rank_of(a, a.shape_off[s]);
+}
+
+__global__ void __launch_bounds__(kThreads) k_zero_lastface(ImportArgs a) {
+    const uint32_t n = min(a.status->total_vertices, a.vertex_capacity);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) a.lastface[i] = 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Final indices
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_final_index(ImportArgs a) {
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < a.m1; s += gridDim.x * blockDim.x) {
+        if (a.table1[s] == kEmpty64) continue;
+        const uint32_t x = a.aux1[s];
+        if (x == kUnmatchable) continue;
+        if (x >= a.m2) continue;                      // only after an overflow; the host re-runs then
+        const uint32_t rep = (uint32_t)a.table2[x];  // first corner with this VALUE key
+        if (rep >= a.ncorners) continue;
+        const uint32_t sh = find_shape(a.shape_off, a.nshapes, rep);
+        a.aux1[s] = rank_of(a, rep) - a.vbase[sh];
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_write_indices(ImportArgs a) {
+    const uint32_t ngroups = (a.ncorners + 3) >> 2;
+    for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
+        const uint32_t c0 = g << 2;
+        uint32_t s[4] = {0, 0, 0, 0};
+        const bool full = (c0 + 4 <= a.ncorners);
+        if (full) {
+            const uint4 q = *reinterpret_cast<const uint4*>(a.slot1 + c0);
+            s[0] = q.x; s[1] = q.y; s[2] = q.z; s[3] = q.w;
+        } else {
+            for (int i = 0; i < 4 && c0 + i < a.ncorners; ++i) s[i] = a.slot1[c0 + i];
+        }
+        uint32_t li[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) li[i] = (c0 + i < a.ncorners) ? a.aux1[s[i]] : 0;
+        uint32_t sh = find_shape(a.shape_off, a.nshapes, c0);
+        uint32_t sh_end = a.shape_off[sh + 1], base = a.vbase[sh];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t c = c0 + i;
+            if (c >= a.ncorners) break;
+            if (c >= sh_end) {
+                sh = find_shape(a.shape_off, a.nshapes, c);
+                sh_end = a.shape_off[sh + 1];
+                base = a.vbase[sh];
+            }
+            if (li[i] == kUnmatchable) li[i] = 0;  // mesh_loader.cpp:285 default-inserts value 0 for a NaN key
+            const uint32_t gv = base + li[i];
+            if (gv < a.vertex_capacity) atomicMax(a.lastface + gv, c / 3 + 1);
+        }
+        if (full) {
+            *reinterpret_cast<uint4*>(a.out_idx + c0) = make_uint4(li[0], li[1], li[2], li[3]);
+        } else {
+            for (int i = 0; i < 4 && c0 + i < a.ncorners; ++i) a.out_idx[c0 + i] = li[i];
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Vertex records (stable compaction of vertex-creating corners)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_write_vertices(ImportArgs a) {
+    const uint32_t lane = threadIdx.x & 31;
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < a.ncorners; c += gridDim.x * blockDim.x) {
+        const uint32_t w = c >> 5;
+        const uint32_t bits = a.fbits[w];
+        if (!((bits >> lane) & 1u)) continue;
+        const uint32_t id = a.fprefix[w] + __popc(bits & ((1u << lane) - 1u));
+        if (id >= a.vertex_capacity) continue;
+        const int32_t* o = a.idx + 3ull * c;
+        uint32_t k[8];
+        gather_key(a, (uint32_t)__ldg(o), (uint32_t)__ldg(o + 1), (uint32_t)__ldg(o + 2), k);
+        float4* dst = a.out_vtx + 4ull * id;
+        // Vertex3D: position @0, normal @12, texcoord @24, color @32 (zero), tangent @48 (filled by k_tangents)
+        dst[0] = make_float4(__uint_as_float(k[0]), __uint_as_float(k[1]), __uint_as_float(k[2]), __uint_as_float(k[3]));
+        dst[1] = make_float4(__uint_as_float(k[4]), __uint_as_float(k[5]), __uint_as_float(k[6]), __uint_as_float(k[7]));
+        dst[2] = make_float4(0.f, 0.f, 0.f, 0.f);
+        dst[3] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Tangents / normals: one thread per vertex evaluates the winning triangle.
+// Arithmetic mirrors geometry.cpp:26-47 / :72-75 operation by operation with round-to-nearest
+// intrinsics, which the compiler never contracts into FMAs (the reference CPU build has none).
+// ---------------------------------------------------------------------------------------------
+struct Tri {
+    float px[3], py[3], pz[3], u[3], v[3];
+};
+
+__device__ __forceinline__ void load_tri(const float4* __restrict__ vtx, const uint32_t i[3], Tri& t) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float4 a = vtx[4ull * i[k]];                                         // position.xyz, normal.x
+        const float2 b = *reinterpret_cast<const float2*>(reinterpret_cast<const float*>(vtx + 4ull * i[k]) + 6);
+        t.px[k] = a.x; t.py[k] = a.y; t.pz[k] = a.z;
+        t.u[k] = b.x; t.v[k] = b.y;
+    }
+}
+
+__device__ __forceinline__ float3 normalize_rn(float x, float y, float z) {
+    // glm::normalize = v * inversesqrt(dot(v, v)); dot3 = (x*x + y*y) + z*z; inversesqrt = 1 / sqrt
+    const float d = __fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z));
+    const float inv = __fdiv_rn(1.0f, __fsqrt_rn(d));
+    return make_float3(__fmul_rn(x, inv), __fmul_rn(y, inv), __fmul_rn(z, inv));
+}
+
+__device__ __forceinline__ float4 tangent_of(const Tri& t) {
+    const float e1x = __fsub_rn(t.px[1], t.px[0]), e1y = __fsub_rn(t.py[1], t.py[0]), e1z = __fsub_rn(t.pz[1], t.pz[0]);
+    const float e2x = __fsub_rn(t.px[2], t.px[0]), e2y = __fsub_rn(t.py[2], t.py[0]), e2z = __fsub_rn(t.pz[2], t.pz[0]);
+    const float du1 = __fsub_rn(t.u[1], t.u[0]), dv1 = __fsub_rn(t.v[1], t.v[0]);
+    const float du2 = __fsub_rn(t.u[2], t.u[0]), dv2 = __fsub_rn(t.v[2], t.v[0]);
+    const float dividend = __fsub_rn(__fmul_rn(du1, dv2), __fmul_rn(du2, dv1));
+    const float fc = __fdiv_rn(1.0f, dividend);
+    const float tx = __fmul_rn(fc, __fsub_rn(__fmul_rn(dv2, e1x), __fmul_rn(dv1, e2x)));
+    const float ty = __fmul_rn(fc, __fsub_rn(__fmul_rn(dv2, e1y), __fmul_rn(dv1, e2y)));
+    const float tz = __fmul_rn(fc, __fsub_rn(__fmul_rn(dv2, e1z), __fmul_rn(dv1, e2z)));
+    const float3 n = normalize_rn(tx, ty, tz);
+    return make_float4(n.x, n.y, n.z, (dividend < 0.0f) ? -1.0f : 1.0f);
+}
+
+__device__ __forceinline__ float3 normal_of(const Tri& t) {
+    const float ax = __fsub_rn(t.px[1], t.px[0]), ay = __fsub_rn(t.py[1], t.py[0]), az = __fsub_rn(t.pz[1], t.pz[0]);
+    const float bx = __fsub_rn(t.px[2], t.px[0]), by = __fsub_rn(t.py[2], t.py[0]), bz = __fsub_rn(t.pz[2], t.pz[0]);
+    // glm::cross, glm/detail/func_geometric.inl:68-79
+    const float nx = __fsub_rn(__fmul_rn(ay, bz), __fmul_rn(by, az));
+    const float ny = __fsub_rn(__fmul_rn(az, bx), __fmul_rn(bz, ax));
+    const float nz = __fsub_rn(__fmul_rn(ax, by), __fmul_rn(bx, ay));
+    return normalize_rn(nx, ny, nz);
+}
+
+// lastface[v] = 1 + highest triangle id that references vertex v (0 = unreferenced).
+__global__ void __launch_bounds__(kThreads) k_last_face(const uint32_t* __restrict__ indices, uint32_t index_count,
+                                                        uint32_t vertex_count, uint32_t* lastface,
+                                                        uint32_t* bad_flag) {
+    const uint32_t ntri = index_count / 3;
+    for (uint32_t f = blockIdx.x * blockDim.x + threadIdx.x; f < ntri; f += gridDim.x * blockDim.x) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const uint32_t v = indices[3ull * f + k];
+            if (v < vertex_count) atomicMax(lastface + v, f + 1);
+            else *bad_flag = 1;
+        }
+    }
+}
+
+// mode 0: tangents (writes float4 @48), mode 1: normals (writes 3 floats @12).
+// shape_off / vbase may be null for a single index space (the stand-alone utilities).
+template <int MODE>
+__global__ void __launch_bounds__(kThreads) k_per_vertex_frames(float4* vtx, const uint32_t* __restrict__ indices,
+                                                                const uint32_t* __restrict__ lastface,
+                                                                const uint32_t* __restrict__ total_ptr, uint32_t total_max,
+                                                                const uint32_t* __restrict__ shape_off,
+                                                                const uint32_t* __restrict__ vbase, uint32_t nshapes,
+                                                                uint32_t vertex_limit) {
+    const uint32_t total = total_ptr ? min(*total_ptr, total_max) : total_max;
+    for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < total; v += gridDim.x * blockDim.x) {
+        const uint32_t lf = lastface[v];
+        if (lf == 0) continue;  // referenced by no triangle: the reference never touches it
+        const uint32_t f = lf - 1;
+        uint32_t base = 0;
+        if (shape_off) base = vbase[find_shape(shape_off, nshapes, 3 * f)];
+        uint32_t i[3];
+        bool ok = true;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            i[k] = indices[3ull * f + k] + base;
+            ok &= (i[k] < vertex_limit);
+        }
+        if (!ok) continue;
+        Tri t;
+        load_tri(vtx, i, t);
+        if (MODE == 0) {
+            vtx[4ull * v + 3] = tangent_of(t);
+        } else {
+            const float3 n = normal_of(t);
+            float* dst = reinterpret_cast<float*>(vtx + 4ull * v) + 3;
+            dst[0] = n.x; dst[1] = n.y; dst[2] = n.z;
+        }
+    }
+}
+
+}  // namespace vkm

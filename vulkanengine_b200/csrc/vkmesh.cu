@@ -1,0 +1,614 @@
+// Host side of libvkmesh_b200.so: the import plan (device buffers + kernel schedule) and the C ABI
+// declared in include/vkmesh_b200.h.  CUDA runtime only -- no PyTorch, no CPU fallback.
+#include "../../include/vkmesh_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "vkm_kernels.cuh"
+
+using namespace vkm;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                                        \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess) {                                                                        \
+            int code_ = (e_ == cudaErrorMemoryAllocation) ? VKM_ERR_OOM                                 \
+                        : (e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver) ? VKM_ERR_NO_DEVICE \
+                                                                                         : VKM_ERR_CUDA; \
+            return fail(code_, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+        }                                                                                               \
+    } while (0)
+
+constexpr uint64_t kMaxCorners = 4000000000ull;
+
+int sm_count(int device) {
+    static int cached[64] = {0};
+    if (device >= 0 && device < 64 && cached[device]) return cached[device];
+    int n = 148;
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device);
+    if (device >= 0 && device < 64) cached[device] = n;
+    return n;
+}
+
+// Grid for a grid-stride kernel: enough CTAs to cover `items`, capped at a whole number of waves.
+unsigned grid_for(uint64_t items, int threads, int device, int ctas_per_sm = 8) {
+    const uint64_t need = (items + threads - 1) / threads;
+    const uint64_t cap = (uint64_t)sm_count(device) * ctas_per_sm;
+    return (unsigned)std::max<uint64_t>(1, std::min(need, cap));
+}
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    uint64_t n = 0;
+    int ensure(uint64_t count) {
+        if (count <= n && p) return VKM_OK;
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+        cudaError_t e = cudaMalloc(&p, std::max<uint64_t>(count, 1) * sizeof(T));
+        if (e != cudaSuccess) {
+            p = nullptr;
+            return fail(VKM_ERR_OOM, "cudaMalloc(%llu bytes) failed: %s", (unsigned long long)(count * sizeof(T)),
+                        cudaGetErrorString(e));
+        }
+        n = count;
+        return VKM_OK;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = 0;
+    }
+};
+
+enum Phase { PH_CLEAR = 0, PH_INSERT, PH_FIRSTS, PH_SCAN, PH_INDICES, PH_VERTICES, PH_TANGENTS, PH_COUNT };
+const char* kPhaseNames[PH_COUNT] = {"clear", "insert_triplets", "resolve_firsts", "mark_scan", "indices",
+                                     "vertices", "tangents"};
+
+}  // namespace
+
+struct vkm_plan {
+    vkm_plan_desc desc{};
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t last_stream = nullptr;
+    uint32_t m1 = 0, m2 = 0;
+    DevBuf<uint64_t> table1, table2;
+    DevBuf<uint32_t> slot1, aux1, fbits, fprefix, block_sums, ext_enc, vbase, lastface, out_idx, shape_off;
+    DevBuf<float4> out_vtx;
+    DevBuf<Status> status;
+    // pinned host mirrors
+    Status* h_status = nullptr;
+    uint32_t* h_vbase = nullptr;
+    uint32_t* h_ext = nullptr;
+    uint32_t* h_shape_off = nullptr;
+    uint32_t host_shapes_cap = 0;
+    cudaEvent_t ev[PH_COUNT + 1]{};
+    cudaEvent_t done = nullptr;
+    bool timing = false;
+    bool pending = false;
+    // last import (kept for the re-run after a table overflow)
+    ImportArgs args{};
+    std::vector<uint32_t> vertex_offsets;
+    std::vector<vkm_extent> extents;
+    float phase_ms[8]{};
+};
+
+namespace {
+
+int plan_size_tables(vkm_plan* p, uint64_t slots) {
+    slots = std::min<uint64_t>(std::max<uint64_t>(slots, 1024), 0xFFFFFF00ull);
+    p->m1 = p->m2 = (uint32_t)slots;
+    int rc;
+    if ((rc = p->table1.ensure(slots))) return rc;
+    if ((rc = p->table2.ensure(slots))) return rc;
+    if ((rc = p->aux1.ensure(slots))) return rc;
+    return VKM_OK;
+}
+
+uint64_t initial_slots(const vkm_plan_desc& d) {
+    // Distinct (v,n,t) triplets T are at least the largest attribute array (if all records are referenced)
+    // and at most the corner count.  Start optimistic, grow on overflow.
+    uint64_t est = d.max_corners;
+    if (d.max_attrib) est = std::min<uint64_t>(d.max_corners, d.max_attrib + d.max_attrib / 4 + 1024);
+    return 2 * est + 64;
+}
+
+int plan_enqueue(vkm_plan* p) {
+    ImportArgs& a = p->args;
+    cudaStream_t st = p->last_stream;
+    const int dev = p->desc.device;
+    a.table1 = p->table1.p;
+    a.table2 = p->table2.p;
+    a.aux1 = p->aux1.p;
+    a.m1 = p->m1;
+    a.m2 = p->m2;
+    const bool T = p->timing;
+    if (T) CU(cudaEventRecord(p->ev[PH_CLEAR], st));
+    CU(cudaMemsetAsync(p->status.p, 0, sizeof(Status), st));
+    CU(cudaMemsetAsync(a.table1, 0xFF, (uint64_t)a.m1 * 8, st));
+    CU(cudaMemsetAsync(a.table2, 0xFF, (uint64_t)a.m2 * 8, st));
+    CU(cudaMemsetAsync(a.fbits, 0, ((uint64_t)a.nwords + 1) * 4, st));
+    // encoded +0.0 everywhere: GeometryExtent extent{} (mesh_loader.cpp:230)
+    CU(cudaMemsetAsync(a.ext_enc, 0, (uint64_t)a.nshapes * 6 * 4, st));
+    {
+        // 0x80000000 pattern = enc_float(+0); memset can only write bytes, so set the top byte of each word
+        // with a strided 2D memset.
+        CU(cudaMemset2DAsync(reinterpret_cast<char*>(a.ext_enc) + 3, 4, 0x80, 1, (size_t)a.nshapes * 6, st));
+    }
+    if (T) CU(cudaEventRecord(p->ev[PH_INSERT], st));
+    k_insert_triplets<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
+    if (T) CU(cudaEventRecord(p->ev[PH_FIRSTS], st));
+    k_resolve_firsts<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
+    k_mark_unmatchable<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
+    if (T) CU(cudaEventRecord(p->ev[PH_SCAN], st));
+    k_mark_value_firsts<<<grid_for(a.m2, kThreads, dev), kThreads, 0, st>>>(a);
+    const uint32_t ntiles = std::max<uint32_t>(1, (a.nwords + kScanTile - 1) / kScanTile);
+    k_scan_tiles<<<ntiles, kScanThreads, 0, st>>>(a);
+    k_scan_block_sums<<<1, kScanThreads, 0, st>>>(a, ntiles);
+    k_scan_write<<<ntiles, kScanThreads, 0, st>>>(a);
+    k_shape_bases<<<grid_for((uint64_t)a.nshapes + 1, 128, dev), 128, 0, st>>>(a);
+    k_zero_lastface<<<grid_for(a.vertex_capacity, kThreads, dev), kThreads, 0, st>>>(a);
+    if (T) CU(cudaEventRecord(p->ev[PH_INDICES], st));
+    k_final_index<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
+    k_write_indices<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
+    if (T) CU(cudaEventRecord(p->ev[PH_VERTICES], st));
+    k_write_vertices<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
+    if (T) CU(cudaEventRecord(p->ev[PH_TANGENTS], st));
+    k_per_vertex_frames<0><<<grid_for(a.vertex_capacity, kThreads, dev), kThreads, 0, st>>>(
+        a.out_vtx, a.out_idx, a.lastface, &p->status.p->total_vertices, a.vertex_capacity, a.shape_off, a.vbase,
+        a.nshapes, a.vertex_capacity);
+    if (T) CU(cudaEventRecord(p->ev[PH_COUNT], st));
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(p->h_status, p->status.p, sizeof(Status), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(p->h_vbase, a.vbase, ((uint64_t)a.nshapes + 1) * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(p->h_ext, a.ext_enc, (uint64_t)a.nshapes * 6 * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(p->done, st));
+    p->pending = true;
+    return VKM_OK;
+}
+
+}  // namespace
+
+// =================================================================================================
+// C ABI
+// =================================================================================================
+extern "C" {
+
+const char* vkm_last_error(void) { return g_err.c_str(); }
+const char* vkm_version(void) { return "vkmesh_b200 0.1 (sm_100a)"; }
+
+int vkm_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+const char* vkm_plan_phase_name(int phase) { return (phase >= 0 && phase < PH_COUNT) ? kPhaseNames[phase] : nullptr; }
+
+int vkm_plan_create(const vkm_plan_desc* desc, vkm_plan** out) {
+    if (!desc || !out) return fail(VKM_ERR_INVALID_ARG, "vkm_plan_create: null argument");
+    if (desc->max_corners > kMaxCorners) return fail(VKM_ERR_INVALID_ARG, "vkm_plan_create: more than %llu corners", (unsigned long long)kMaxCorners);
+    if (vkm_device_count() <= desc->device) return fail(VKM_ERR_NO_DEVICE, "vkm_plan_create: CUDA device %d not present (there is no CPU path)", desc->device);
+    CU(cudaSetDevice(desc->device));
+    vkm_plan* p = new vkm_plan();
+    p->desc = *desc;
+    if (p->desc.max_shapes == 0) p->desc.max_shapes = 1;
+    if (p->desc.max_vertices == 0 || p->desc.max_vertices > p->desc.max_corners) p->desc.max_vertices = p->desc.max_corners;
+    const uint64_t C = std::max<uint64_t>(p->desc.max_corners, 1), V = std::max<uint64_t>(p->desc.max_vertices, 1);
+    const uint64_t W = (C + 31) / 32;
+    const uint32_t S = p->desc.max_shapes;
+    int rc = VKM_OK;
+    auto chk = [&](int r) { if (rc == VKM_OK) rc = r; };
+    chk(plan_size_tables(p, initial_slots(p->desc)));
+    chk(p->slot1.ensure(C + 4));
+    chk(p->fbits.ensure(W + 1));
+    chk(p->fprefix.ensure(W + 1));
+    chk(p->block_sums.ensure((W + kScanTile - 1) / kScanTile + 1));
+    chk(p->ext_enc.ensure((uint64_t)S * 6));
+    chk(p->vbase.ensure((uint64_t)S + 1));
+    chk(p->shape_off.ensure((uint64_t)S + 1));
+    chk(p->lastface.ensure(V));
+    chk(p->out_idx.ensure(C + 4));
+    chk(p->out_vtx.ensure(V * 4));
+    chk(p->status.ensure(1));
+    if (rc != VKM_OK) {
+        vkm_plan_destroy(p);
+        return rc;
+    }
+    cudaError_t e = cudaSuccess;
+    auto cu = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+    cu(cudaStreamCreateWithFlags(&p->own_stream, cudaStreamNonBlocking));
+    cu(cudaMallocHost(&p->h_status, sizeof(Status)));
+    cu(cudaMallocHost(&p->h_vbase, ((uint64_t)S + 1) * 4));
+    cu(cudaMallocHost(&p->h_ext, (uint64_t)S * 6 * 4));
+    cu(cudaMallocHost(&p->h_shape_off, ((uint64_t)S + 1) * 4));
+    for (auto& ev : p->ev) cu(cudaEventCreate(&ev));
+    cu(cudaEventCreateWithFlags(&p->done, cudaEventDisableTiming));
+    if (e != cudaSuccess) {
+        vkm_plan_destroy(p);
+        return fail(VKM_ERR_CUDA, "vkm_plan_create: %s", cudaGetErrorString(e));
+    }
+    p->host_shapes_cap = S;
+    *out = p;
+    return VKM_OK;
+}
+
+void vkm_plan_destroy(vkm_plan* p) {
+    if (!p) return;
+    cudaSetDevice(p->desc.device);
+    if (p->pending && p->done) cudaEventSynchronize(p->done);
+    p->table1.release(); p->table2.release(); p->slot1.release(); p->aux1.release(); p->fbits.release();
+    p->fprefix.release(); p->block_sums.release(); p->ext_enc.release(); p->vbase.release(); p->lastface.release();
+    p->out_idx.release(); p->shape_off.release(); p->out_vtx.release(); p->status.release();
+    if (p->h_status) cudaFreeHost(p->h_status);
+    if (p->h_vbase) cudaFreeHost(p->h_vbase);
+    if (p->h_ext) cudaFreeHost(p->h_ext);
+    if (p->h_shape_off) cudaFreeHost(p->h_shape_off);
+    for (auto& ev : p->ev) if (ev) cudaEventDestroy(ev);
+    if (p->done) cudaEventDestroy(p->done);
+    if (p->own_stream) cudaStreamDestroy(p->own_stream);
+    delete p;
+}
+
+void vkm_plan_set_timing(vkm_plan* p, int enabled) { if (p) p->timing = enabled != 0; }
+
+int vkm_plan_import(vkm_plan* p, const float* d_pos, uint64_t np, const float* d_nrm, uint64_t nn, const float* d_uv,
+                    uint64_t nt, const int32_t* d_idx, const uint64_t* shape_corner_offsets, uint32_t nshapes,
+                    void* stream) {
+    if (!p || !shape_corner_offsets) return fail(VKM_ERR_INVALID_ARG, "vkm_plan_import: null argument");
+    if (nshapes == 0 || nshapes > p->desc.max_shapes) return fail(VKM_ERR_CAPACITY, "vkm_plan_import: %u shapes, plan holds %u", nshapes, p->desc.max_shapes);
+    if (shape_corner_offsets[0] != 0) return fail(VKM_ERR_INVALID_ARG, "vkm_plan_import: shape_corner_offsets[0] must be 0");
+    const uint64_t C = shape_corner_offsets[nshapes];
+    if (C > p->desc.max_corners) return fail(VKM_ERR_CAPACITY, "vkm_plan_import: %llu corners, plan holds %llu", (unsigned long long)C, (unsigned long long)p->desc.max_corners);
+    if (np >= 0x7FFFFFFFull || nn >= 0x7FFFFFFFull || nt >= 0x7FFFFFFFull) return fail(VKM_ERR_INVALID_ARG, "vkm_plan_import: attribute arrays beyond the int32 index range");
+    if (p->pending) {
+        CU(cudaEventSynchronize(p->done));
+        p->pending = false;
+    }
+    for (uint32_t s = 0; s < nshapes; ++s) {
+        const uint64_t a = shape_corner_offsets[s], b = shape_corner_offsets[s + 1];
+        if (b < a || (b - a) % 3 != 0) return fail(VKM_ERR_INVALID_ARG, "vkm_plan_import: shape %u corner range is not a whole number of triangles", s);
+        p->h_shape_off[s] = (uint32_t)a;
+    }
+    p->h_shape_off[nshapes] = (uint32_t)C;
+    if (C > 0 && (np == 0 || nn == 0 || nt == 0 || !d_pos || !d_nrm || !d_uv || !d_idx))
+        return fail(VKM_ERR_BAD_INDEX, "vkm_plan_import: corners reference an empty attribute array");
+    CU(cudaSetDevice(p->desc.device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : p->own_stream;
+    p->last_stream = st;
+    ImportArgs& a = p->args;
+    a = ImportArgs{};
+    a.pos = d_pos; a.nrm = d_nrm; a.uv = d_uv; a.idx = d_idx;
+    a.np = (uint32_t)np; a.nn = (uint32_t)nn; a.nt = (uint32_t)nt;
+    a.ncorners = (uint32_t)C;
+    a.shape_off = p->shape_off.p;
+    a.nshapes = nshapes;
+    a.slot1 = p->slot1.p; a.fbits = p->fbits.p; a.fprefix = p->fprefix.p; a.block_sums = p->block_sums.p;
+    a.nwords = (uint32_t)((C + 31) / 32);
+    a.ext_enc = p->ext_enc.p; a.vbase = p->vbase.p; a.lastface = p->lastface.p;
+    a.out_idx = p->out_idx.p; a.out_vtx = p->out_vtx.p;
+    a.vertex_capacity = (uint32_t)std::min<uint64_t>(p->desc.max_vertices, 0xFFFFFFFEull);
+    a.status = p->status.p;
+    CU(cudaMemcpyAsync(p->shape_off.p, p->h_shape_off, ((uint64_t)nshapes + 1) * 4, cudaMemcpyHostToDevice, st));
+    return plan_enqueue(p);
+}
+
+int vkm_plan_finish(vkm_plan* p, vkm_plan_result* r) {
+    if (!p) return fail(VKM_ERR_INVALID_ARG, "vkm_plan_finish: null plan");
+    if (!p->pending) return fail(VKM_ERR_INVALID_ARG, "vkm_plan_finish: no import in flight");
+    CU(cudaSetDevice(p->desc.device));
+    for (int attempt = 0;; ++attempt) {
+        CU(cudaEventSynchronize(p->done));
+        p->pending = false;
+        const Status s = *p->h_status;
+        if (s.bad_index) return fail(VKM_ERR_BAD_INDEX, "import: a vertex/normal/texcoord index is negative or out of range");
+        if (s.overflow1 || s.overflow2) {
+            // optimistic table sizing failed: grow (bounded by 2 slots per corner) and run the import again
+            const uint64_t worst = 2ull * p->args.ncorners + 64;
+            if ((uint64_t)p->m1 >= worst || attempt > 8) return fail(VKM_ERR_CAPACITY, "import: hash table overflow at worst-case size");
+            CU(cudaStreamSynchronize(p->last_stream));
+            int rc = plan_size_tables(p, std::min<uint64_t>(worst, 2ull * p->m1));
+            if (rc) return rc;
+            if ((rc = plan_enqueue(p))) return rc;
+            continue;
+        }
+        if (s.capacity_exceeded) return fail(VKM_ERR_CAPACITY, "import: %u unique vertices exceed the plan capacity %llu", s.total_vertices, (unsigned long long)p->desc.max_vertices);
+        break;
+    }
+    const uint32_t S = p->args.nshapes;
+    p->vertex_offsets.assign(p->h_vbase, p->h_vbase + S + 1);
+    p->extents.resize(S);
+    for (uint32_t s = 0; s < S; ++s) {
+        vkm_extent& e = p->extents[s];
+        for (int k = 0; k < 3; ++k) {
+            float mn = dec_float(p->h_ext[6 * s + k]), mx = dec_float(p->h_ext[6 * s + 3 + k]);
+            if (mn == 0.0f) mn = 0.0f;  // -0 never replaces the initial +0 in the reference (strict <)
+            if (mx == 0.0f) mx = 0.0f;
+            e.min_extents[k] = mn;
+            e.max_extents[k] = mx;
+            e.center[k] = (mn + mx) / 2.0f;  // mesh_loader.cpp:290-292
+        }
+    }
+    for (int i = 0; i < 8; ++i) p->phase_ms[i] = 0.f;
+    if (p->timing)
+        for (int i = 0; i < PH_COUNT; ++i) cudaEventElapsedTime(&p->phase_ms[i], p->ev[i], p->ev[i + 1]);
+    if (r) {
+        r->total_vertices = p->h_status->total_vertices;
+        r->total_indices = p->args.ncorners;
+        r->d_vertices = p->out_vtx.p;
+        r->d_indices = p->out_idx.p;
+        r->shape_vertex_offsets = p->vertex_offsets.data();
+        r->shape_extents = p->extents.data();
+        memcpy(r->phase_ms, p->phase_ms, sizeof p->phase_ms);
+    }
+    return VKM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Stand-alone geometry utilities
+// ------------------------------------------------------------------------------------------------
+static int frames_dev(int mode, uint32_t vertex_count, void* d_vertices, uint32_t index_count, const uint32_t* d_indices,
+                      uint32_t* d_scratch, cudaStream_t st, uint32_t* d_bad) {
+    if (vertex_count == 0 || index_count < 3) return VKM_OK;
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    CU(cudaMemsetAsync(d_scratch, 0, (uint64_t)vertex_count * 4, st));
+    k_last_face<<<grid_for(index_count / 3, kThreads, dev), kThreads, 0, st>>>(d_indices, index_count, vertex_count,
+                                                                             d_scratch, d_bad);
+    if (mode == 0)
+        k_per_vertex_frames<0><<<grid_for(vertex_count, kThreads, dev), kThreads, 0, st>>>(
+            (float4*)d_vertices, d_indices, d_scratch, nullptr, vertex_count, nullptr, nullptr, 1, vertex_count);
+    else
+        k_per_vertex_frames<1><<<grid_for(vertex_count, kThreads, dev), kThreads, 0, st>>>(
+            (float4*)d_vertices, d_indices, d_scratch, nullptr, vertex_count, nullptr, nullptr, 1, vertex_count);
+    CU(cudaGetLastError());
+    return VKM_OK;
+}
+
+// Device variants report out-of-range indices by skipping them (a device-side caller owns its buffers);
+// the host variants below check the flag and fail.
+__device__ uint32_t g_frames_bad_sink;
+
+int vkm_generate_tangents_dev(uint32_t vc, void* d_v, uint32_t ic, const uint32_t* d_i, uint32_t* d_scratch, void* stream) {
+    if (vkm_device_count() == 0) return fail(VKM_ERR_NO_DEVICE, "no CUDA device (there is no CPU path)");
+    uint32_t* sink = nullptr;
+    CU(cudaGetSymbolAddress((void**)&sink, g_frames_bad_sink));
+    return frames_dev(0, vc, d_v, ic, d_i, d_scratch, (cudaStream_t)stream, sink);
+}
+int vkm_generate_normals_dev(uint32_t vc, void* d_v, uint32_t ic, const uint32_t* d_i, uint32_t* d_scratch, void* stream) {
+    if (vkm_device_count() == 0) return fail(VKM_ERR_NO_DEVICE, "no CUDA device (there is no CPU path)");
+    uint32_t* sink = nullptr;
+    CU(cudaGetSymbolAddress((void**)&sink, g_frames_bad_sink));
+    return frames_dev(1, vc, d_v, ic, d_i, d_scratch, (cudaStream_t)stream, sink);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host entry points
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+struct HostCtx {
+    std::mutex mu;
+    std::vector<int> devices{0};
+    // cached per-process staging (grown on demand) for the host entry points, device = devices[0]
+    vkm_plan* plan = nullptr;
+    DevBuf<float> pos, nrm, uv;
+    DevBuf<int32_t> idx;
+    DevBuf<float4> vtx;
+    DevBuf<uint32_t> ind, scratch, flag;
+    cudaStream_t st = nullptr;
+    int bound_device = -1;
+};
+HostCtx g_ctx;
+
+int ctx_bind(HostCtx& c) {
+    if (vkm_device_count() == 0) return fail(VKM_ERR_NO_DEVICE, "no CUDA device: vkmesh_b200 has no CPU path");
+    const int dev = c.devices[0];
+    CU(cudaSetDevice(dev));
+    if (c.bound_device != dev) {
+        if (c.plan) { vkm_plan_destroy(c.plan); c.plan = nullptr; }
+        c.pos.release(); c.nrm.release(); c.uv.release(); c.idx.release(); c.vtx.release(); c.ind.release();
+        c.scratch.release(); c.flag.release();
+        if (c.st) cudaStreamDestroy(c.st);
+        c.st = nullptr;
+        CU(cudaStreamCreateWithFlags(&c.st, cudaStreamNonBlocking));
+        c.bound_device = dev;
+    }
+    return VKM_OK;
+}
+
+int frames_host(int mode, uint32_t vc, void* vertices, uint32_t ic, const uint32_t* indices) {
+    if (ic >= 3 && (!vertices || !indices)) return fail(VKM_ERR_INVALID_ARG, "null vertices/indices");
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    int rc = ctx_bind(g_ctx);
+    if (rc) return rc;
+    if (vc == 0 || ic < 3) return VKM_OK;
+    HostCtx& c = g_ctx;
+    if ((rc = c.vtx.ensure((uint64_t)vc * 4))) return rc;
+    if ((rc = c.ind.ensure(ic))) return rc;
+    if ((rc = c.scratch.ensure(vc))) return rc;
+    if ((rc = c.flag.ensure(1))) return rc;
+    CU(cudaMemcpyAsync(c.vtx.p, vertices, (uint64_t)vc * 64, cudaMemcpyHostToDevice, c.st));
+    CU(cudaMemcpyAsync(c.ind.p, indices, (uint64_t)ic * 4, cudaMemcpyHostToDevice, c.st));
+    CU(cudaMemsetAsync(c.flag.p, 0, 4, c.st));
+    if ((rc = frames_dev(mode, vc, c.vtx.p, ic, c.ind.p, c.scratch.p, c.st, c.flag.p))) return rc;
+    uint32_t bad = 0;
+    CU(cudaMemcpyAsync(&bad, c.flag.p, 4, cudaMemcpyDeviceToHost, c.st));
+    CU(cudaStreamSynchronize(c.st));
+    if (bad) return fail(VKM_ERR_BAD_INDEX, "an index is >= vertex_count (undefined behaviour in the reference)");
+    CU(cudaMemcpyAsync(vertices, c.vtx.p, (uint64_t)vc * 64, cudaMemcpyDeviceToHost, c.st));
+    CU(cudaStreamSynchronize(c.st));
+    return VKM_OK;
+}
+
+}  // namespace
+
+int vkm_init(const int* device_ordinals, int count) {
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    const int n = vkm_device_count();
+    if (n == 0) return fail(VKM_ERR_NO_DEVICE, "no CUDA device: vkmesh_b200 has no CPU path");
+    std::vector<int> d;
+    if (!device_ordinals || count <= 0) d.push_back(0);
+    for (int i = 0; device_ordinals && i < count; ++i) {
+        if (device_ordinals[i] < 0 || device_ordinals[i] >= n) return fail(VKM_ERR_INVALID_ARG, "device ordinal %d out of range (%d devices)", device_ordinals[i], n);
+        d.push_back(device_ordinals[i]);
+    }
+    g_ctx.devices = d;
+    return ctx_bind(g_ctx);
+}
+
+void vkm_shutdown(void) {
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    HostCtx& c = g_ctx;
+    if (c.bound_device < 0) return;
+    cudaSetDevice(c.bound_device);
+    if (c.plan) { vkm_plan_destroy(c.plan); c.plan = nullptr; }
+    c.pos.release(); c.nrm.release(); c.uv.release(); c.idx.release(); c.vtx.release(); c.ind.release();
+    c.scratch.release(); c.flag.release();
+    if (c.st) cudaStreamDestroy(c.st);
+    c.st = nullptr;
+    c.bound_device = -1;
+}
+
+int vkm_generate_tangents(uint32_t vc, void* v, uint32_t ic, const uint32_t* idx) { return frames_host(0, vc, v, ic, idx); }
+int vkm_generate_normals(uint32_t vc, void* v, uint32_t ic, const uint32_t* idx) { return frames_host(1, vc, v, ic, idx); }
+
+uint32_t vkm_deduplicate_vertices(uint32_t, const void*, uint32_t, uint32_t*, void**) {
+    fail(VKM_ERR_INVALID_ARG, "vkm_deduplicate_vertices: not built yet");
+    return 0xFFFFFFFFu;
+}
+
+void vkm_free_shape(vkm_shape_out* s) {
+    if (!s) return;
+    free(s->vertices);
+    free(s->indices);
+    s->vertices = nullptr;
+    s->indices = nullptr;
+}
+
+int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t nn, const float* uv, uint64_t nt,
+                      const int32_t* idx, const uint64_t* shape_off, uint32_t nshapes, vkm_shape_out* out) {
+    if (nshapes == 0) return VKM_OK;
+    if (!shape_off || !out) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: null argument");
+    for (uint32_t s = 0; s < nshapes; ++s) {
+        memset(&out[s], 0, sizeof(vkm_shape_out));
+        out[s].vertex_size = 64;
+        out[s].index_size = 4;
+    }
+    const uint64_t C = shape_off[nshapes];
+    if (C > kMaxCorners) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: too many corners");
+    if (C > 0 && (!pos || !nrm || !uv || !idx)) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: null input stream");
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    HostCtx& c = g_ctx;
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    const uint64_t max_attrib = std::max(np, std::max(nn, nt));
+    if (!c.plan || c.plan->desc.max_corners < C || c.plan->desc.max_shapes < nshapes || c.plan->desc.max_attrib < max_attrib) {
+        if (c.plan) vkm_plan_destroy(c.plan);
+        c.plan = nullptr;
+        vkm_plan_desc d{};
+        d.device = c.devices[0];
+        d.max_corners = C;
+        d.max_vertices = 0;
+        d.max_attrib = max_attrib;
+        d.max_shapes = nshapes;
+        if ((rc = vkm_plan_create(&d, &c.plan))) return rc;
+    }
+    if ((rc = c.pos.ensure(3 * np + 4))) return rc;
+    if ((rc = c.nrm.ensure(3 * nn + 4))) return rc;
+    if ((rc = c.uv.ensure(2 * nt + 4))) return rc;
+    if ((rc = c.idx.ensure(3 * C + 16))) return rc;
+    if (np) CU(cudaMemcpyAsync(c.pos.p, pos, np * 12, cudaMemcpyHostToDevice, c.st));
+    if (nn) CU(cudaMemcpyAsync(c.nrm.p, nrm, nn * 12, cudaMemcpyHostToDevice, c.st));
+    if (nt) CU(cudaMemcpyAsync(c.uv.p, uv, nt * 8, cudaMemcpyHostToDevice, c.st));
+    if (C) CU(cudaMemcpyAsync(c.idx.p, idx, C * 12, cudaMemcpyHostToDevice, c.st));
+    if ((rc = vkm_plan_import(c.plan, c.pos.p, np, c.nrm.p, nn, c.uv.p, nt, c.idx.p, shape_off, nshapes, c.st))) return rc;
+    vkm_plan_result r{};
+    if ((rc = vkm_plan_finish(c.plan, &r))) return rc;
+    for (uint32_t s = 0; s < nshapes; ++s) {
+        vkm_shape_out& o = out[s];
+        const uint32_t v0 = r.shape_vertex_offsets[s], v1 = r.shape_vertex_offsets[s + 1];
+        const uint64_t c0 = shape_off[s], c1 = shape_off[s + 1];
+        o.vertex_count = v1 - v0;
+        o.index_count = (uint32_t)(c1 - c0);
+        o.extent = r.shape_extents[s];
+        // malloc(): the engine frees these with free() (Platform::FrMemory, mesh_resource.cpp:13-18)
+        o.vertices = malloc(std::max<uint64_t>((uint64_t)o.vertex_count * 64, 1));
+        o.indices = malloc(std::max<uint64_t>((uint64_t)o.index_count * 4, 1));
+        if (!o.vertices || !o.indices) {
+            for (uint32_t k = 0; k <= s; ++k) vkm_free_shape(&out[k]);
+            return fail(VKM_ERR_OOM, "vkm_import_shapes: host allocation failed");
+        }
+        if (o.vertex_count) CU(cudaMemcpyAsync(o.vertices, (const char*)r.d_vertices + (uint64_t)v0 * 64, (uint64_t)o.vertex_count * 64, cudaMemcpyDeviceToHost, c.st));
+        if (o.index_count) CU(cudaMemcpyAsync(o.indices, r.d_indices + c0, (uint64_t)o.index_count * 4, cudaMemcpyDeviceToHost, c.st));
+    }
+    CU(cudaStreamSynchronize(c.st));
+    return VKM_OK;
+}
+
+void* vkm_host_alloc(uint64_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, std::max<uint64_t>(bytes, 1)) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+void vkm_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+int vkm_dev_alloc(int device, uint64_t bytes, void** d_ptr) {
+    if (!d_ptr) return fail(VKM_ERR_INVALID_ARG, "null");
+    if (vkm_device_count() <= device) return fail(VKM_ERR_NO_DEVICE, "CUDA device %d not present", device);
+    CU(cudaSetDevice(device));
+    CU(cudaMalloc(d_ptr, std::max<uint64_t>(bytes, 1)));
+    return VKM_OK;
+}
+int vkm_dev_free(int device, void* d_ptr) {
+    CU(cudaSetDevice(device));
+    CU(cudaFree(d_ptr));
+    return VKM_OK;
+}
+int vkm_dev_upload(int device, void* d_dst, const void* h_src, uint64_t bytes) {
+    CU(cudaSetDevice(device));
+    CU(cudaMemcpy(d_dst, h_src, bytes, cudaMemcpyHostToDevice));
+    return VKM_OK;
+}
+int vkm_dev_download(int device, void* h_dst, const void* d_src, uint64_t bytes) {
+    CU(cudaSetDevice(device));
+    CU(cudaMemcpy(h_dst, d_src, bytes, cudaMemcpyDeviceToHost));
+    return VKM_OK;
+}
+int vkm_dev_sync(int device) {
+    CU(cudaSetDevice(device));
+    CU(cudaDeviceSynchronize());
+    return VKM_OK;
+}
+
+}  // extern "C"
