@@ -1,0 +1,383 @@
+#!/usr/bin/env python
+"""Benchmark of the mesh-import geometry path (BASELINE.json metric: mesh triangles/s, % HBM peak).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+One "step" = one pass of the hot path (face expansion -> first-occurrence vertex dedup -> bounding box
+-> tangents) over one synthetic mesh per GPU, inputs resident in HBM, outputs left in HBM.  Multi-GPU
+(torchrun, one rank per GPU): every rank imports its own independent mesh, no data-path collective
+("weak" scaling); the only communication is the timing barrier / max over ranks.
+
+The JSON line carries, besides the base contract: `roofline` (dominant kernel, algorithmic bytes over
+CUDA-event time against the measured HBM copy bandwidth), `pipeline_roofline` (the whole step against
+SURVEY.md 8(d)'s B_alg), `cpu_baseline` (the reference's own code, oracle/_ref, timed on this host on
+a bounded sample), `e2e` (the same import through the host C-ABI entry vkm_import_shapes, H2D and D2H
+inside the timed region), `gpu_launches` and `clocks`.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "mesh triangles/sec (dedup+normals+tangents)"
+UNIT = "triangles/s"
+KERNELS_PER_STEP = 13  # our kernels per import (memset nodes not counted); see vkmesh.cu plan_enqueue
+FALLBACK_HBM_GBS = 6650.0
+
+WORKLOADS = {
+    # name: (grid n, permute seed, description)
+    "highdup16m": (2896, None, "synthetic 16.8M-triangle high-duplication grid mesh (valence 6), configs[2]"),
+    "grid1m": (708, None, "synthetic 1.0M-triangle grid mesh, configs[1]"),
+    "highdup16m_perm": (2896, 0x5EED0003, "16.8M-triangle grid, seeded random face order (locality defeated)"),
+    "grid64m": (5793, None, "67.1M-triangle grid (configs[4] base, without injections)"),
+}
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.proc = None
+        self.t0 = self.t1 = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu=timestamp,{self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                         stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def mark(self, which):
+        setattr(self, which, time.time())
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        self.f.flush()
+        self.f.seek(0)
+        rows = [r.strip().split(", ") for r in self.f.read().splitlines() if r.strip()]
+        self.f.close()
+        os.unlink(self.f.name)
+        import datetime
+
+        sm, mx, reasons, inside = [], [], set(), []
+        for r in rows:
+            if len(r) < 10:
+                continue
+            try:
+                ts = datetime.datetime.strptime(r[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                clk, cmax = float(r[2]), float(r[3])
+            except ValueError:
+                continue
+            rec = (ts, clk, cmax, r[6:10])
+            sm.append(rec)
+            if self.t0 and self.t1 and self.t0 - 0.05 <= ts <= self.t1 + 0.05:
+                inside.append(rec)
+        use = inside if len(inside) >= 2 else sm
+        if not use:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for rec in use:
+            for nme, val in zip(names, rec[3]):
+                if val.strip().lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median([u[1] for u in use])), "sm_max_mhz": float(max(u[2] for u in use)),
+                "reasons": sorted(reasons), "samples": len(use), "in_timed_region": len(inside) >= 2}
+
+
+# ------------------------------------------------------------------------------------------ reference arm
+def cpu_reference_run(n: int, repeats: int, threads: int = 1):
+    """Times the reference's own import loop (oracle/_ref, else the plain-C port) on a grid(n) mesh.
+    Returns (triangles per second over all threads, kind)."""
+    from oracle import port, refcpu
+    from vulkanengine_b200 import synth
+
+    if refcpu.available():
+        fn, kind = refcpu.import_arrays, "reference"
+    else:
+        fn, kind = port.import_arrays, "port"
+    m = synth.grid(n)
+
+    def work():
+        for _ in range(repeats):
+            fn(m.pos, m.nrm, m.uv, m.idx, m.shape_offsets, collect=False)
+
+    t0 = time.perf_counter()
+    if threads <= 1:
+        work()
+    else:
+        ts = [threading.Thread(target=work) for _ in range(threads)]  # ctypes releases the GIL
+        [t.start() for t in ts]
+        [t.join() for t in ts]
+    dt = time.perf_counter() - t0
+    return m.triangles * repeats * max(threads, 1) / dt, kind, m.triangles, dt
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    threads = max(1, min(world, cores))
+    # bounded sample: keep the whole run near two minutes at ~0.8 M triangles/s/thread
+    budget = 120.0 / max(1, args.steps + args.warmup)
+    tris = int(min(4.2e6, max(2.0e5, 0.8e6 * budget)))
+    n = max(16, int((tris / 2) ** 0.5))
+    if args.warmup:
+        cpu_reference_run(n, args.warmup, threads)
+    # K timed steps; mesh generation happens before the clock starts inside cpu_reference_run
+    value, kind, ntri, dt = cpu_reference_run(n, args.steps, threads)
+    sample = (f"grid n={n} ({2 * n * n} triangles, same valence-6 family as the GPU workload) per step and per "
+              f"thread; {threads} thread(s) = one independent mesh per GPU rank (the reference imports one mesh "
+              f"on one thread); g++ -O2 -ffp-contract=off")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32+f32", "data": "synthetic",
+        "config": {"workload": args.workload, "description": WORKLOADS[args.workload][2], "cpu_sample_grid_n": n},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ our arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="highdup16m", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world == 1 and args.gpus > 1:
+        # launched without torchrun: re-exec under torchrun so that there is one process per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 2000), os.path.abspath(__file__),
+               *sys.argv[1:]]
+        sys.exit(subprocess.call(cmd))
+
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    from vulkanengine_b200 import capi, synth
+
+    if not torch.cuda.is_available() or capi.lib().vkm_device_count() == 0:
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = local_rank
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            t = torch.zeros(1, device="cuda")
+            dist.all_reduce(t)
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    n, perm, desc = WORKLOADS[args.workload]
+    # independent meshes per rank: same shape family, different placement
+    mesh = synth.grid(n, permute_seed=perm, offset=(float(rank), -float(rank), 0.5 * rank), scale=1.0 + 0.25 * rank)
+    F, C = mesh.triangles, mesh.corners
+    max_attrib = max(len(mesh.pos), len(mesh.nrm), len(mesh.uv))
+
+    d_pos, d_nrm, d_uv, d_idx = (capi.DeviceArray(dev, a) for a in (mesh.pos, mesh.nrm, mesh.uv, mesh.idx))
+    plan = capi.Plan(dev, C, max_attrib=max_attrib, max_vertices=max_attrib + max_attrib // 8 + 1024, max_shapes=1)
+    stream = torch.cuda.Stream(device=dev)
+
+    def step():
+        plan.import_async(d_pos.ptr, len(mesh.pos), d_nrm.ptr, len(mesh.nrm), d_uv.ptr, len(mesh.uv), d_idx.ptr,
+                          mesh.shape_offsets, stream=stream.cuda_stream)
+
+    sampler = ClockSampler(dev)
+    sampler.start()
+    for _ in range(args.warmup):
+        step()
+        r = plan.finish()
+    U = int(r.total_vertices)
+
+    # ---- timed region: K steps, device time (CUDA events on the launching stream), max over ranks
+    # The K imports are queued back to back on one stream (no host sync between steps); the plan records
+    # CUDA events between its phases for every import (a ring of event sets) and finish() averages them.
+    plan.set_timing(True)
+    barrier()
+    sampler.mark("t0")
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    r = plan.finish()  # waits for the last import, checks the device status word
+    barrier()
+    sampler.mark("t1")
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.stop()
+    plan.set_timing(False)
+    phase_ms = np.array(list(r.phase_ms))
+    total_tris = sum_over_ranks(float(F)) * args.steps
+    value = total_tris / (ms_total * 1e-3)
+    ms_per_step = ms_total / args.steps
+
+    # ---- roofline
+    peak, peak_src = hbm_peak()
+    b_alg = mesh.algorithmic_bytes(U)
+    names = plan.phase_names()
+    # algorithmic bytes each phase is the first to read / the one to write (they sum to B_alg)
+    share = {
+        "insert_triplets": 36 * F,                                             # the (v,n,t) index stream
+        "resolve_firsts": mesh.pos.nbytes + mesh.nrm.nbytes + mesh.uv.nbytes + 36,  # attribute arrays + extent
+        "indices": 12 * F,                                                     # u32 index buffer
+        "vertices": 48 * U,                                                    # Vertex3D minus tangent
+        "tangents": 16 * U,                                                    # tangent column
+        "clear": 0, "mark_scan": 0,
+    }
+    dom = int(np.argmax(phase_ms[: len(names)]))
+    dom_name = names[dom]
+    kernels = {nm: {"ms": float(phase_ms[i]), "algorithmic_bytes": int(share.get(nm, 0))} for i, nm in enumerate(names)}
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(args.workload, {}).get(dom_name)
+        except Exception:
+            traffic = None
+    dom_bytes = share.get(dom_name, 0)
+    dom_ach = dom_bytes / (phase_ms[dom] * 1e-3) / 1e9 if phase_ms[dom] > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": dom_name, "achieved": dom_ach, "peak": peak, "unit": "GB/s",
+                "frac": dom_ach / peak, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": int(dom_bytes), "ms_per_launch": float(phase_ms[dom]),
+                "share_of_step": float(phase_ms[dom] / max(phase_ms.sum(), 1e-9))}
+    pipe_ach = b_alg / (ms_per_step * 1e-3) / 1e9
+    pipeline_roofline = {"bound": "hbm", "achieved": pipe_ach, "peak": peak, "unit": "GB/s", "frac": pipe_ach / peak,
+                         "algorithmic_bytes_per_step": int(b_alg), "bytes_per_triangle": b_alg / F, "kernels": kernels}
+
+    # ---- end to end through the host C-ABI entry point (pinned host inputs, H2D + kernels + D2H per step)
+    import ctypes as C_
+
+    L = capi.lib()
+    plan.destroy()
+    for d in (d_pos, d_nrm, d_uv, d_idx):
+        d.free()
+
+    def pinned_copy(a):
+        p = L.vkm_host_alloc(a.nbytes)
+        if not p:
+            raise SystemExit("pinned host allocation failed")
+        C_.memmove(p, a.ctypes.data, a.nbytes)
+        return p
+
+    h_pos, h_nrm, h_uv, h_idx = (pinned_copy(a) for a in (mesh.pos, mesh.nrm, mesh.uv, mesh.idx))
+    so = np.ascontiguousarray(mesh.shape_offsets, np.uint64)
+    out = (capi.ShapeOut * 1)()
+
+    def e2e_step():
+        rc = L.vkm_import_shapes(h_pos, len(mesh.pos), h_nrm, len(mesh.nrm), h_uv, len(mesh.uv), h_idx, so.ctypes.data,
+                                 1, out)
+        if rc:
+            raise SystemExit("vkm_import_shapes failed: " + L.vkm_last_error().decode())
+        nv, ni = out[0].vertex_count, out[0].index_count
+        L.vkm_free_shape(C_.byref(out[0]))
+        return nv, ni
+
+    capi.init([dev])
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        nv, ni = e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    e2e_value = sum_over_ranks(float(F)) * args.e2e_steps / e2e_s
+    e2e = {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(mesh.input_bytes()),
+           "d2h_bytes_per_step": int(64 * nv + 4 * ni), "ms_per_step": e2e_s / args.e2e_steps * 1e3,
+           "api": "vkm_import_shapes (host pointers; inputs pinned, outputs malloc'd as the engine expects)"}
+    for p in (h_pos, h_nrm, h_uv, h_idx):
+        L.vkm_host_free(p)
+
+    # ---- CPU baseline (rank 0, N = 1 only): the reference's own code on this host, bounded sample
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        ncpu = 1448  # 4.19M triangles, about 5-10 s of single-thread work
+        v, kind, ntri, dt = cpu_reference_run(ncpu, 1, 1)
+        cpu_baseline = {"value": v, "unit": UNIT, "cores": 1, "kind": kind,
+                        "sample": f"grid n={ncpu} ({ntri} triangles, same family as the workload), one pass, {dt:.1f} s; "
+                                  f"the reference imports a mesh on one thread; host has {os.cpu_count()} logical CPUs; "
+                                  f"g++ -O2 -ffp-contract=off"}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u32+f32", "data": "synthetic",
+            "config": {"workload": args.workload, "description": desc, "triangles_per_gpu": F, "corners_per_gpu": C,
+                       "unique_vertices_per_gpu": U, "meshes_per_gpu": 1, "parallelism": f"{world} independent mesh(es), one per GPU, no collective",
+                       "l2": f"inputs {mesh.input_bytes() / 1e6:.0f} MB + outputs {(64 * U + 4 * C) / 1e6:.0f} MB per step exceed the 126 MB L2 (no flush needed)"
+                             if mesh.input_bytes() > 200e6 else "working set below L2 size: numbers are L2-warm"},
+            "roofline": roofline, "pipeline_roofline": pipeline_roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
+            "gpu_launches": KERNELS_PER_STEP * args.steps, "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -104,9 +104,15 @@ struct vkm_plan {
     Status* h_status = nullptr;
     uint32_t* h_vbase = nullptr;
     uint32_t* h_ext = nullptr;
-    uint32_t* h_shape_off = nullptr;
-    uint32_t host_shapes_cap = 0;
-    cudaEvent_t ev[PH_COUNT + 1]{};
+    uint32_t* h_shape_off = nullptr;  // pinned, kRing x (max_shapes + 1): one staging row per in-flight import
+    // ring of per-import phase events, so that imports can be queued back to back and still be timed
+    static constexpr int kRing = 32;
+    cudaEvent_t ev[kRing][PH_COUNT + 1]{};
+    bool ev_used[kRing]{};     // phase events of the slot hold an unharvested measurement
+    bool slot_busy[kRing]{};   // the slot's import may still be running (its end event was recorded)
+    uint64_t seq = 0;
+    double phase_sum[8]{};
+    uint32_t phase_n = 0;
     cudaEvent_t done = nullptr;
     bool timing = false;
     bool pending = false;
@@ -137,17 +143,33 @@ uint64_t initial_slots(const vkm_plan_desc& d) {
     return 2 * est + 64;
 }
 
+// Folds the phase times of ring slot `slot` into the running sums (waits for that import to finish).
+void plan_harvest(vkm_plan* p, int slot) {
+    if (!p->ev_used[slot]) return;
+    if (cudaEventSynchronize(p->ev[slot][PH_COUNT]) == cudaSuccess) {
+        for (int i = 0; i < PH_COUNT; ++i) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, p->ev[slot][i], p->ev[slot][i + 1]) == cudaSuccess) p->phase_sum[i] += ms;
+        }
+        p->phase_n++;
+    }
+    p->ev_used[slot] = false;
+}
+
 int plan_enqueue(vkm_plan* p) {
     ImportArgs& a = p->args;
     cudaStream_t st = p->last_stream;
     const int dev = p->desc.device;
+    const int slot = (int)(p->seq % vkm_plan::kRing);
+    cudaEvent_t* ev = p->ev[slot];
+    if (p->timing) p->ev_used[slot] = true;
     a.table1 = p->table1.p;
     a.table2 = p->table2.p;
     a.aux1 = p->aux1.p;
     a.m1 = p->m1;
     a.m2 = p->m2;
     const bool T = p->timing;
-    if (T) CU(cudaEventRecord(p->ev[PH_CLEAR], st));
+    if (T) CU(cudaEventRecord(ev[PH_CLEAR], st));
     CU(cudaMemsetAsync(p->status.p, 0, sizeof(Status), st));
     CU(cudaMemsetAsync(a.table1, 0xFF, (uint64_t)a.m1 * 8, st));
     CU(cudaMemsetAsync(a.table2, 0xFF, (uint64_t)a.m2 * 8, st));
@@ -159,12 +181,12 @@ int plan_enqueue(vkm_plan* p) {
         // with a strided 2D memset.
         CU(cudaMemset2DAsync(reinterpret_cast<char*>(a.ext_enc) + 3, 4, 0x80, 1, (size_t)a.nshapes * 6, st));
     }
-    if (T) CU(cudaEventRecord(p->ev[PH_INSERT], st));
+    if (T) CU(cudaEventRecord(ev[PH_INSERT], st));
     k_insert_triplets<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
-    if (T) CU(cudaEventRecord(p->ev[PH_FIRSTS], st));
+    if (T) CU(cudaEventRecord(ev[PH_FIRSTS], st));
     k_resolve_firsts<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
     k_mark_unmatchable<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
-    if (T) CU(cudaEventRecord(p->ev[PH_SCAN], st));
+    if (T) CU(cudaEventRecord(ev[PH_SCAN], st));
     k_mark_value_firsts<<<grid_for(a.m2, kThreads, dev), kThreads, 0, st>>>(a);
     const uint32_t ntiles = std::max<uint32_t>(1, (a.nwords + kScanTile - 1) / kScanTile);
     k_scan_tiles<<<ntiles, kScanThreads, 0, st>>>(a);
@@ -172,16 +194,18 @@ int plan_enqueue(vkm_plan* p) {
     k_scan_write<<<ntiles, kScanThreads, 0, st>>>(a);
     k_shape_bases<<<grid_for((uint64_t)a.nshapes + 1, 128, dev), 128, 0, st>>>(a);
     k_zero_lastface<<<grid_for(a.vertex_capacity, kThreads, dev), kThreads, 0, st>>>(a);
-    if (T) CU(cudaEventRecord(p->ev[PH_INDICES], st));
+    if (T) CU(cudaEventRecord(ev[PH_INDICES], st));
     k_final_index<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
     k_write_indices<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
-    if (T) CU(cudaEventRecord(p->ev[PH_VERTICES], st));
+    if (T) CU(cudaEventRecord(ev[PH_VERTICES], st));
     k_write_vertices<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
-    if (T) CU(cudaEventRecord(p->ev[PH_TANGENTS], st));
+    if (T) CU(cudaEventRecord(ev[PH_TANGENTS], st));
     k_per_vertex_frames<0><<<grid_for(a.vertex_capacity, kThreads, dev), kThreads, 0, st>>>(
         a.out_vtx, a.out_idx, a.lastface, &p->status.p->total_vertices, a.vertex_capacity, a.shape_off, a.vbase,
         a.nshapes, a.vertex_capacity);
-    if (T) CU(cudaEventRecord(p->ev[PH_COUNT], st));
+    CU(cudaEventRecord(ev[PH_COUNT], st));
+    p->slot_busy[slot] = true;
+    p->seq++;
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(p->h_status, p->status.p, sizeof(Status), cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(p->h_vbase, a.vbase, ((uint64_t)a.nshapes + 1) * 4, cudaMemcpyDeviceToHost, st));
@@ -248,14 +272,13 @@ int vkm_plan_create(const vkm_plan_desc* desc, vkm_plan** out) {
     cu(cudaMallocHost(&p->h_status, sizeof(Status)));
     cu(cudaMallocHost(&p->h_vbase, ((uint64_t)S + 1) * 4));
     cu(cudaMallocHost(&p->h_ext, (uint64_t)S * 6 * 4));
-    cu(cudaMallocHost(&p->h_shape_off, ((uint64_t)S + 1) * 4));
-    for (auto& ev : p->ev) cu(cudaEventCreate(&ev));
+    cu(cudaMallocHost(&p->h_shape_off, (uint64_t)vkm_plan::kRing * ((uint64_t)S + 1) * 4));
+    for (auto& ring : p->ev) for (auto& ev : ring) cu(cudaEventCreate(&ev));
     cu(cudaEventCreateWithFlags(&p->done, cudaEventDisableTiming));
     if (e != cudaSuccess) {
         vkm_plan_destroy(p);
         return fail(VKM_ERR_CUDA, "vkm_plan_create: %s", cudaGetErrorString(e));
     }
-    p->host_shapes_cap = S;
     *out = p;
     return VKM_OK;
 }
@@ -271,7 +294,7 @@ void vkm_plan_destroy(vkm_plan* p) {
     if (p->h_vbase) cudaFreeHost(p->h_vbase);
     if (p->h_ext) cudaFreeHost(p->h_ext);
     if (p->h_shape_off) cudaFreeHost(p->h_shape_off);
-    for (auto& ev : p->ev) if (ev) cudaEventDestroy(ev);
+    for (auto& ring : p->ev) for (auto& ev : ring) if (ev) cudaEventDestroy(ev);
     if (p->done) cudaEventDestroy(p->done);
     if (p->own_stream) cudaStreamDestroy(p->own_stream);
     delete p;
@@ -288,20 +311,25 @@ int vkm_plan_import(vkm_plan* p, const float* d_pos, uint64_t np, const float* d
     const uint64_t C = shape_corner_offsets[nshapes];
     if (C > p->desc.max_corners) return fail(VKM_ERR_CAPACITY, "vkm_plan_import: %llu corners, plan holds %llu", (unsigned long long)C, (unsigned long long)p->desc.max_corners);
     if (np >= 0x7FFFFFFFull || nn >= 0x7FFFFFFFull || nt >= 0x7FFFFFFFull) return fail(VKM_ERR_INVALID_ARG, "vkm_plan_import: attribute arrays beyond the int32 index range");
-    if (p->pending) {
+    cudaStream_t st = stream ? (cudaStream_t)stream : p->own_stream;
+    if (p->pending && st != p->last_stream) {  // same-stream imports are ordered by the stream itself
         CU(cudaEventSynchronize(p->done));
         p->pending = false;
     }
     for (uint32_t s = 0; s < nshapes; ++s) {
         const uint64_t a = shape_corner_offsets[s], b = shape_corner_offsets[s + 1];
         if (b < a || (b - a) % 3 != 0) return fail(VKM_ERR_INVALID_ARG, "vkm_plan_import: shape %u corner range is not a whole number of triangles", s);
-        p->h_shape_off[s] = (uint32_t)a;
     }
-    p->h_shape_off[nshapes] = (uint32_t)C;
+    // claim this import's ring slot: its staging row and events are free once the import that last used it is done
+    const int slot = (int)(p->seq % vkm_plan::kRing);
+    if (p->ev_used[slot]) plan_harvest(p, slot);
+    else if (p->slot_busy[slot]) CU(cudaEventSynchronize(p->ev[slot][PH_COUNT]));
+    p->slot_busy[slot] = false;
+    uint32_t* stage = p->h_shape_off + (uint64_t)slot * ((uint64_t)p->desc.max_shapes + 1);
+    for (uint32_t s = 0; s <= nshapes; ++s) stage[s] = (uint32_t)shape_corner_offsets[s];
     if (C > 0 && (np == 0 || nn == 0 || nt == 0 || !d_pos || !d_nrm || !d_uv || !d_idx))
         return fail(VKM_ERR_BAD_INDEX, "vkm_plan_import: corners reference an empty attribute array");
     CU(cudaSetDevice(p->desc.device));
-    cudaStream_t st = stream ? (cudaStream_t)stream : p->own_stream;
     p->last_stream = st;
     ImportArgs& a = p->args;
     a = ImportArgs{};
@@ -316,7 +344,7 @@ int vkm_plan_import(vkm_plan* p, const float* d_pos, uint64_t np, const float* d
     a.out_idx = p->out_idx.p; a.out_vtx = p->out_vtx.p;
     a.vertex_capacity = (uint32_t)std::min<uint64_t>(p->desc.max_vertices, 0xFFFFFFFEull);
     a.status = p->status.p;
-    CU(cudaMemcpyAsync(p->shape_off.p, p->h_shape_off, ((uint64_t)nshapes + 1) * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(p->shape_off.p, stage, ((uint64_t)nshapes + 1) * 4, cudaMemcpyHostToDevice, st));
     return plan_enqueue(p);
 }
 
@@ -356,9 +384,13 @@ int vkm_plan_finish(vkm_plan* p, vkm_plan_result* r) {
             e.center[k] = (mn + mx) / 2.0f;  // mesh_loader.cpp:290-292
         }
     }
-    for (int i = 0; i < 8; ++i) p->phase_ms[i] = 0.f;
-    if (p->timing)
-        for (int i = 0; i < PH_COUNT; ++i) cudaEventElapsedTime(&p->phase_ms[i], p->ev[i], p->ev[i + 1]);
+    // average phase times over the imports queued since the previous finish
+    for (int slot = 0; slot < vkm_plan::kRing; ++slot) plan_harvest(p, slot);
+    for (int i = 0; i < 8; ++i) {
+        p->phase_ms[i] = p->phase_n ? (float)(p->phase_sum[i] / p->phase_n) : 0.f;
+        p->phase_sum[i] = 0.0;
+    }
+    p->phase_n = 0;
     if (r) {
         r->total_vertices = p->h_status->total_vertices;
         r->total_indices = p->args.ncorners;
