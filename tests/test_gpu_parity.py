@@ -125,6 +125,24 @@ def test_all_unique_corners_grows_tables():
     assert_shapes_equal(capi.import_shapes(pos, nrm, uv, idx, so), port.import_arrays(pos, nrm, uv, idx, so))
 
 
+def test_many_triplets_per_attribute_record_falls_back_to_scrambled_table():
+    # tiny attribute arrays, tens of thousands of distinct (v,n,t) combinations: the coherent (key-attribute)
+    # addressing clusters, the library must switch to the scrambled table and grow it
+    rng = np.random.default_rng(6)
+    n = 30000
+    pos = rng.standard_normal((64, 3)).astype(np.float32)
+    nrm = rng.standard_normal((64, 3)).astype(np.float32)
+    uv = rng.random((64, 2)).astype(np.float32)
+    idx = rng.integers(0, 64, (n, 3)).astype(np.int32)
+    so = np.array([0, n], np.uint64)
+    want = port.import_arrays(pos, nrm, uv, idx, so)
+    assert len(want[0].vertices) > 25000
+    assert_shapes_equal(capi.import_shapes(pos, nrm, uv, idx, so), want)
+    # and a coherent mesh right afterwards still works (the host entry retries coherent addressing per call)
+    g = synth.grid(33)
+    assert_shapes_equal(gpu_of(g), oracle_of(g))
+
+
 def test_value_duplicates_with_distinct_triplets_merge():
     # every attribute record exists twice: 8 different triplets per vertex value
     g = synth.grid(20)

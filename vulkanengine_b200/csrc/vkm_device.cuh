@@ -6,7 +6,8 @@
 
 namespace vkm {
 
-constexpr uint64_t kEmpty64 = ~0ull;          // empty hash slot
+constexpr uint64_t kEmpty64 = ~0ull;          // empty slot of the (tagged, 64-bit) value table
+constexpr uint32_t kEmpty32 = 0xFFFFFFFFu;     // empty slot of the (32-bit) triplet table
 constexpr uint32_t kUnmatchable = 0xFFFFFFFFu; // aux marker: key holds NaN/Inf and never matches anything
 constexpr int kMaxProbe = 2048;
 
@@ -33,8 +34,12 @@ struct ImportArgs {
     const uint32_t* shape_off;  // nshapes + 1 corner offsets
     uint32_t nshapes;
     // scratch
-    uint64_t* table1;  // triplet table: (tag << 32 | first corner)
+    uint32_t* table1;  // triplet table: first (lowest) corner that carries the slot's (shape, v, n, t)
     uint32_t m1;
+    uint32_t t1_mode;   // 0: locality-preserving home slot (key attribute index * scale), 1: scrambled hash
+    uint32_t t1_sel;    // which of v / n / t is the key attribute (the largest attribute array)
+    uint32_t t1_scale;  // slots per key-attribute record
+    uint32_t* cand;     // [nwords + 1] bit c set <=> corner c may be the first of its triplet (set by K1)
     uint64_t* table2;  // value table:   (tag << 32 | first corner)
     uint32_t m2;
     uint32_t* slot1;   // [ncorners] slot of every corner in table1
@@ -68,6 +73,33 @@ __device__ __forceinline__ uint64_t hash_triplet(uint32_t v, uint32_t n, uint32_
     return mix64(a ^ mix64(b + 0x9e3779b97f4a7c15ull));
 }
 
+// Range reduction without a power-of-two table: floor(x * m / 2^32).
+__device__ __forceinline__ uint32_t reduce32(uint32_t x, uint32_t m) { return __umulhi(x, m); }
+
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+    x ^= x >> 16;
+    x *= 0x7feb352du;
+    x ^= x >> 15;
+    x *= 0x846ca68bu;
+    x ^= x >> 16;
+    return x;
+}
+
+// Home slot of a triplet.  Mode 0 keeps the order of the key attribute's indices, so that a mesh whose faces
+// are stored coherently touches the table coherently (neighbouring corners -> neighbouring slots -> shared
+// sectors); the other two indices only pick one of `scale` sub-slots.  Mode 1 is a full scramble, used when
+// mode 0 clusters (many distinct triplets per key record).
+__device__ __forceinline__ uint32_t home_slot(const ImportArgs& a, uint32_t v, uint32_t n, uint32_t t, uint32_t sh) {
+    if (a.t1_mode == 0) {
+        const uint32_t key = a.t1_sel == 0 ? v : (a.t1_sel == 1 ? n : t);
+        const uint32_t o1 = a.t1_sel == 0 ? n : v;
+        const uint32_t o2 = a.t1_sel == 2 ? n : t;
+        const uint32_t sub = (mix32(o1 * 0x9E3779B1u ^ o2 * 0x85EBCA77u ^ sh) >> 8) % a.t1_scale;
+        return key * a.t1_scale + sub;  // < np|nn|nt * scale <= m1 (host guarantees no 32-bit overflow)
+    }
+    return reduce32((uint32_t)hash_triplet(v, n, t, sh), a.m1);
+}
+
 __device__ __forceinline__ uint64_t hash_key8(const uint32_t k[8], uint32_t shape) {
     uint64_t h = mix64(((uint64_t)k[0] | ((uint64_t)k[1] << 32)) + 0x9e3779b97f4a7c15ull * (shape + 1));
     h = mix64(h ^ ((uint64_t)k[2] | ((uint64_t)k[3] << 32)));
@@ -75,9 +107,6 @@ __device__ __forceinline__ uint64_t hash_key8(const uint32_t k[8], uint32_t shap
     h = mix64(h ^ ((uint64_t)k[6] | ((uint64_t)k[7] << 32)));
     return h;
 }
-
-// Range reduction without a power-of-two table: floor(x * m / 2^32).
-__device__ __forceinline__ uint32_t reduce32(uint32_t x, uint32_t m) { return __umulhi(x, m); }
 
 // Largest s with shape_off[s] <= c (empty shapes are skipped because the search is an upper bound).
 __device__ __forceinline__ uint32_t find_shape(const uint32_t* __restrict__ shape_off, uint32_t nshapes, uint32_t c) {

@@ -24,30 +24,37 @@ constexpr int kThreads = 256;
 
 // ---------------------------------------------------------------------------------------------
 // K1: triplet insert.  Each thread owns 4 consecutive corners = 48 bytes = three 128-bit loads.
+// The table holds one u32 per slot: the lowest corner id seen so far for the slot's triplet.  Equality
+// is decided exactly, by reading the occupant's own triplet from the index stream (for coherent meshes
+// the occupant is a recent corner, so that read hits L1/L2).  Because corners are visited roughly in
+// order, the occupant is usually already the lowest corner and most duplicates issue no atomic at all.
+// Returns the slot; *cand is set when corner c may be the triplet's first corner.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t insert_triplet(const ImportArgs& a, uint32_t c, uint32_t v, uint32_t n, uint32_t t,
-                                                   uint32_t sh, uint32_t sh_begin, uint32_t sh_end) {
-    const uint64_t h = hash_triplet(v, n, t, sh);
-    const uint32_t tag = (uint32_t)(h >> 32);
-    const uint64_t mine = ((uint64_t)tag << 32) | c;
-    uint32_t s = reduce32((uint32_t)h, a.m1);
+                                                   uint32_t sh, uint32_t sh_begin, uint32_t sh_end, bool* cand) {
+    uint32_t s = home_slot(a, v, n, t, sh);
     for (int probe = 0; probe < kMaxProbe; ++probe) {
-        uint64_t cur = __ldcg(a.table1 + s);
-        if (cur == kEmpty64) {
-            const uint64_t prev = atomicCAS(reinterpret_cast<unsigned long long*>(a.table1 + s), kEmpty64, mine);
-            if (prev == kEmpty64) return s;
+        uint32_t cur = __ldcg(a.table1 + s);
+        if (cur == kEmpty32) {
+            const uint32_t prev = atomicCAS(a.table1 + s, kEmpty32, c);
+            if (prev == kEmpty32) {
+                *cand = true;
+                return s;
+            }
             cur = prev;
         }
-        if ((uint32_t)(cur >> 32) == tag) {
-            const uint32_t occ = (uint32_t)cur;
-            if (occ == c) return s;
-            // Exact check: a slot only ever holds corners of one (shape, v, n, t); tags merely skip gathers.
-            if (occ >= sh_begin && occ < sh_end) {
-                const int32_t* o = a.idx + 3ull * occ;
-                if ((uint32_t)__ldg(o) == v && (uint32_t)__ldg(o + 1) == n && (uint32_t)__ldg(o + 2) == t) {
-                    if (occ > c) atomicMin(reinterpret_cast<unsigned long long*>(a.table1 + s), mine);
-                    return s;
+        if (cur == c) {
+            *cand = true;
+            return s;
+        }
+        if (cur >= sh_begin && cur < sh_end) {
+            const int32_t* o = a.idx + 3ull * cur;
+            if ((uint32_t)__ldg(o) == v && (uint32_t)__ldg(o + 1) == n && (uint32_t)__ldg(o + 2) == t) {
+                if (cur > c) {
+                    atomicMin(a.table1 + s, c);
+                    *cand = true;
                 }
+                return s;
             }
         }
         s = (s + 1 == a.m1) ? 0 : s + 1;
@@ -57,7 +64,8 @@ __device__ __forceinline__ uint32_t insert_triplet(const ImportArgs& a, uint32_t
 }
 
 __global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
-    const uint32_t ngroups = (a.ncorners + 3) >> 2;
+    // whole warps (32 threads = 128 corners = four candidate words) stay in the loop together
+    const uint32_t ngroups = (((a.ncorners + 127) >> 7) << 5);
     for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
         const uint32_t c0 = g << 2;
         int32_t w[12];
@@ -71,9 +79,14 @@ __global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
 #pragma unroll
             for (int i = 0; i < 12; ++i) w[i] = (c0 + i / 3 < a.ncorners) ? __ldg(a.idx + 3ull * c0 + i) : 0;
         }
-        uint32_t sh = find_shape(a.shape_off, a.nshapes, c0);
-        uint32_t sh_begin = a.shape_off[sh], sh_end = a.shape_off[sh + 1];
+        uint32_t sh = 0, sh_begin = 0, sh_end = 0;
+        if (c0 < a.ncorners) {
+            sh = find_shape(a.shape_off, a.nshapes, c0);
+            sh_begin = a.shape_off[sh];
+            sh_end = a.shape_off[sh + 1];
+        }
         uint32_t slots[4];
+        uint32_t nibble = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const uint32_t c = c0 + i;
@@ -89,18 +102,27 @@ __global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
                 a.status->bad_index = 1;
                 continue;
             }
-            slots[i] = insert_triplet(a, c, v, n, t, sh, sh_begin, sh_end);
+            bool cand = false;
+            slots[i] = insert_triplet(a, c, v, n, t, sh, sh_begin, sh_end, &cand);
+            nibble |= (cand ? 1u : 0u) << i;
         }
         if (c0 + 4 <= a.ncorners) {
             *reinterpret_cast<uint4*>(a.slot1 + c0) = make_uint4(slots[0], slots[1], slots[2], slots[3]);
         } else {
             for (int i = 0; i < 4 && c0 + i < a.ncorners; ++i) a.slot1[c0 + i] = slots[i];
         }
+        // candidate bitmap: 8 consecutive lanes hold the 32 bits of one word
+        uint32_t word = nibble << ((threadIdx.x & 7) * 4);
+        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 1);
+        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 2);
+        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 4);
+        if ((threadIdx.x & 7) == 0 && (c0 >> 5) < a.nwords) a.cand[c0 >> 5] = word;
     }
 }
 
 // ---------------------------------------------------------------------------------------------
 // K2: first corner of each distinct triplet -> bounding box, NaN/Inf screening, value-key insert.
+// One thread per candidate word (32 corners); only candidates (about one corner in `valence`) do work.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ bool same_value_key(const ImportArgs& a, uint32_t occ, const uint32_t k[8]) {
     const int32_t* o = a.idx + 3ull * occ;
@@ -128,6 +150,7 @@ __device__ __forceinline__ uint32_t insert_value(const ImportArgs& a, uint32_t c
         if ((uint32_t)(cur >> 32) == tag) {
             const uint32_t occ = (uint32_t)cur;
             if (occ == c) return s;
+            // Exact check: tags only skip gathers; a slot only ever holds corners with one canonical value key.
             if (occ >= sh_begin && occ < sh_end && same_value_key(a, occ, k)) {
                 if (occ > c) atomicMin(reinterpret_cast<unsigned long long*>(a.table2 + s), mine);
                 return s;
@@ -139,31 +162,67 @@ __device__ __forceinline__ uint32_t insert_value(const ImportArgs& a, uint32_t c
     return 0;
 }
 
+__device__ __forceinline__ void box_atomics(uint32_t* e, const uint32_t mn[3], const uint32_t mx[3]) {
+    // bounds converge quickly: read (possibly stale, monotone) values first, atomics only on improvement
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        if (mn[k] < e[k]) atomicMin(e + k, mn[k]);
+        if (mx[k] > e[3 + k]) atomicMax(e + 3 + k, mx[k]);
+    }
+}
+
 __global__ void __launch_bounds__(kThreads) k_resolve_firsts(ImportArgs a) {
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t padded = (a.ncorners + 31) & ~31u;  // whole warps stay in the loop (warp reductions below)
-    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < padded; c += gridDim.x * blockDim.x) {
-        const uint32_t neutral = 0x80000000u;  // enc_float(+0): the reference's box always contains the origin
-        uint32_t mn0 = neutral, mn1 = neutral, mn2 = neutral, mx0 = neutral, mx1 = neutral, mx2 = neutral;
-        uint32_t sh = 0;
-        bool first = false;
-        if (c < a.ncorners) {
-            const uint32_t s = a.slot1[c];
-            first = ((uint32_t)__ldcg(a.table1 + s) == c);
-            sh = find_shape(a.shape_off, a.nshapes, c);
+    const uint32_t padded = (a.nwords + 31) & ~31u;  // whole warps stay in the loop (warp reductions below)
+    const uint32_t neutral = 0x80000000u;            // enc_float(+0): the reference's box always contains the origin
+    for (uint32_t w = blockIdx.x * blockDim.x + threadIdx.x; w < padded; w += gridDim.x * blockDim.x) {
+        uint32_t mn[3] = {neutral, neutral, neutral}, mx[3] = {neutral, neutral, neutral};
+        uint32_t bits = (w < a.nwords) ? a.cand[w] : 0;
+        const uint32_t cbase = w << 5;
+        uint32_t sh = 0, sh_begin = 0, sh_end = 0xFFFFFFFFu;
+        bool word_uniform = true;  // all corners of this word lie in one shape
+        if (w < a.nwords && a.nshapes > 1) {
+            sh = find_shape(a.shape_off, a.nshapes, cbase);
+            sh_begin = a.shape_off[sh];
+            sh_end = a.shape_off[sh + 1];
+            word_uniform = (min(cbase + 31, a.ncorners - 1) < sh_end);
+        } else if (w < a.nwords) {
+            sh_begin = a.shape_off[0];
+            sh_end = a.shape_off[1];
         }
-        if (first) {
+        while (bits) {
+            const uint32_t b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            const uint32_t c = cbase + b;
+            const uint32_t s1 = a.slot1[c];
+            if (__ldcg(a.table1 + s1) != c) continue;  // a lower corner took the slot after K1 looked
+            uint32_t csh = sh, cb = sh_begin, ce = sh_end;
+            if (!word_uniform && c >= sh_end) {
+                csh = find_shape(a.shape_off, a.nshapes, c);
+                cb = a.shape_off[csh];
+                ce = a.shape_off[csh + 1];
+            }
             const int32_t* o = a.idx + 3ull * c;
             uint32_t k[8];
             gather_key(a, (uint32_t)__ldg(o), (uint32_t)__ldg(o + 1), (uint32_t)__ldg(o + 2), k);
             bool bad = false;
 #pragma unroll
             for (int i = 0; i < 8; ++i) bad |= nonfinite_bits(k[i]);
-            // strict </> against NaN never updates the reference's box; +-Inf does
-            if ((k[0] & 0x7FFFFFFFu) <= 0x7F800000u) mn0 = mx0 = enc_float(__uint_as_float(k[0]));
-            if ((k[1] & 0x7FFFFFFFu) <= 0x7F800000u) mn1 = mx1 = enc_float(__uint_as_float(k[1]));
-            if ((k[2] & 0x7FFFFFFFu) <= 0x7F800000u) mn2 = mx2 = enc_float(__uint_as_float(k[2]));
-            const uint32_t s1 = a.slot1[c];
+            uint32_t pmn[3] = {neutral, neutral, neutral}, pmx[3] = {neutral, neutral, neutral};
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                // strict </> against NaN never updates the reference's box; +-Inf does
+                if ((k[i] & 0x7FFFFFFFu) <= 0x7F800000u) pmn[i] = pmx[i] = enc_float(__uint_as_float(k[i]));
+            }
+            if (word_uniform) {
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    mn[i] = min(mn[i], pmn[i]);
+                    mx[i] = max(mx[i], pmx[i]);
+                }
+            } else {
+                box_atomics(a.ext_enc + 6u * csh, pmn, pmx);
+            }
             if (bad) {
                 a.aux1[s1] = kUnmatchable;
                 a.status->has_unmatchable = 1;
@@ -171,29 +230,21 @@ __global__ void __launch_bounds__(kThreads) k_resolve_firsts(ImportArgs a) {
             } else {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) k[i] = canon_bits(k[i]);
-                a.aux1[s1] = insert_value(a, c, k, sh, a.shape_off[sh], a.shape_off[sh + 1]);
+                a.aux1[s1] = insert_value(a, c, k, csh, cb, ce);
             }
         }
-        // bounding box: warp-reduce when the warp sits inside one shape, else per-thread atomics
+        // bounding box: warp-reduce when every lane's word sits inside the same shape, else per-lane atomics
         const uint32_t sh0 = __shfl_sync(0xFFFFFFFFu, sh, 0);
-        const bool uniform = __all_sync(0xFFFFFFFFu, sh == sh0 || c >= a.ncorners);
+        const bool uniform = __all_sync(0xFFFFFFFFu, (sh == sh0 && word_uniform) || w >= a.nwords);
         if (uniform) {
-            mn0 = __reduce_min_sync(0xFFFFFFFFu, mn0);
-            mn1 = __reduce_min_sync(0xFFFFFFFFu, mn1);
-            mn2 = __reduce_min_sync(0xFFFFFFFFu, mn2);
-            mx0 = __reduce_max_sync(0xFFFFFFFFu, mx0);
-            mx1 = __reduce_max_sync(0xFFFFFFFFu, mx1);
-            mx2 = __reduce_max_sync(0xFFFFFFFFu, mx2);
-        }
-        if ((uniform && lane == 0) || (!uniform && first)) {
-            uint32_t* e = a.ext_enc + 6u * (uniform ? sh0 : sh);
-            // bounds converge quickly: read (possibly stale, monotone) values first, atomics only on improvement
-            if (mn0 < e[0]) atomicMin(e + 0, mn0);
-            if (mn1 < e[1]) atomicMin(e + 1, mn1);
-            if (mn2 < e[2]) atomicMin(e + 2, mn2);
-            if (mx0 > e[3]) atomicMax(e + 3, mx0);
-            if (mx1 > e[4]) atomicMax(e + 4, mx1);
-            if (mx2 > e[5]) atomicMax(e + 5, mx2);
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+                mn[i] = __reduce_min_sync(0xFFFFFFFFu, mn[i]);
+                mx[i] = __reduce_max_sync(0xFFFFFFFFu, mx[i]);
+            }
+            if (lane == 0) box_atomics(a.ext_enc + 6u * sh0, mn, mx);
+        } else if (w < a.nwords && word_uniform) {
+            box_atomics(a.ext_enc + 6u * sh, mn, mx);
         }
     }
 }
@@ -315,7 +366,7 @@ __global__ void __launch_bounds__(kThreads) k_zero_lastface(ImportArgs a) {
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads) k_final_index(ImportArgs a) {
     for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < a.m1; s += gridDim.x * blockDim.x) {
-        if (a.table1[s] == kEmpty64) continue;
+        if (a.table1[s] == kEmpty32) continue;
         const uint32_t x = a.aux1[s];
         if (x == kUnmatchable) continue;
         if (x >= a.m2) continue;                      // only after an overflow; the host re-runs then

@@ -95,9 +95,11 @@ struct vkm_plan {
     vkm_plan_desc desc{};
     cudaStream_t own_stream = nullptr;
     cudaStream_t last_stream = nullptr;
-    uint32_t m1 = 0, m2 = 0;
-    DevBuf<uint64_t> table1, table2;
-    DevBuf<uint32_t> slot1, aux1, fbits, fprefix, block_sums, ext_enc, vbase, lastface, out_idx, shape_off;
+    uint32_t m1 = 0, m2 = 0;       // allocated slots
+    uint32_t t1_mode = 0;          // sticky: 0 = locality-preserving triplet table, 1 = scrambled (after clustering)
+    DevBuf<uint32_t> table1;
+    DevBuf<uint64_t> table2;
+    DevBuf<uint32_t> cand, slot1, aux1, fbits, fprefix, block_sums, ext_enc, vbase, lastface, out_idx, shape_off;
     DevBuf<float4> out_vtx;
     DevBuf<Status> status;
     // pinned host mirrors
@@ -166,12 +168,28 @@ int plan_enqueue(vkm_plan* p) {
     a.table1 = p->table1.p;
     a.table2 = p->table2.p;
     a.aux1 = p->aux1.p;
-    a.m1 = p->m1;
     a.m2 = p->m2;
+    {
+        // Triplet table addressing.  Mode 0: home slot = (index into the largest attribute array) * scale, which
+        // keeps the table access pattern as coherent as the mesh's own index order.  Needs scale slots per record.
+        const uint32_t na = std::max(a.np, std::max(a.nn, a.nt));
+        const uint64_t need = 2ull * na + 1024;
+        if (p->t1_mode == 0 && need <= p->m1) {
+            a.t1_mode = 0;
+            a.t1_sel = (a.np >= a.nn && a.np >= a.nt) ? 0u : (a.nn >= a.nt ? 1u : 2u);
+            a.t1_scale = 2;
+            a.m1 = (uint32_t)need;
+        } else {
+            a.t1_mode = 1;
+            a.t1_sel = 0;
+            a.t1_scale = 1;
+            a.m1 = p->m1;
+        }
+    }
     const bool T = p->timing;
     if (T) CU(cudaEventRecord(ev[PH_CLEAR], st));
     CU(cudaMemsetAsync(p->status.p, 0, sizeof(Status), st));
-    CU(cudaMemsetAsync(a.table1, 0xFF, (uint64_t)a.m1 * 8, st));
+    CU(cudaMemsetAsync(a.table1, 0xFF, (uint64_t)a.m1 * 4, st));
     CU(cudaMemsetAsync(a.table2, 0xFF, (uint64_t)a.m2 * 8, st));
     CU(cudaMemsetAsync(a.fbits, 0, ((uint64_t)a.nwords + 1) * 4, st));
     // encoded +0.0 everywhere: GeometryExtent extent{} (mesh_loader.cpp:230)
@@ -252,6 +270,7 @@ int vkm_plan_create(const vkm_plan_desc* desc, vkm_plan** out) {
     auto chk = [&](int r) { if (rc == VKM_OK) rc = r; };
     chk(plan_size_tables(p, initial_slots(p->desc)));
     chk(p->slot1.ensure(C + 4));
+    chk(p->cand.ensure(W + 4));
     chk(p->fbits.ensure(W + 1));
     chk(p->fprefix.ensure(W + 1));
     chk(p->block_sums.ensure((W + kScanTile - 1) / kScanTile + 1));
@@ -287,7 +306,7 @@ void vkm_plan_destroy(vkm_plan* p) {
     if (!p) return;
     cudaSetDevice(p->desc.device);
     if (p->pending && p->done) cudaEventSynchronize(p->done);
-    p->table1.release(); p->table2.release(); p->slot1.release(); p->aux1.release(); p->fbits.release();
+    p->table1.release(); p->table2.release(); p->cand.release(); p->slot1.release(); p->aux1.release(); p->fbits.release();
     p->fprefix.release(); p->block_sums.release(); p->ext_enc.release(); p->vbase.release(); p->lastface.release();
     p->out_idx.release(); p->shape_off.release(); p->out_vtx.release(); p->status.release();
     if (p->h_status) cudaFreeHost(p->h_status);
@@ -338,6 +357,7 @@ int vkm_plan_import(vkm_plan* p, const float* d_pos, uint64_t np, const float* d
     a.ncorners = (uint32_t)C;
     a.shape_off = p->shape_off.p;
     a.nshapes = nshapes;
+    a.cand = p->cand.p;
     a.slot1 = p->slot1.p; a.fbits = p->fbits.p; a.fprefix = p->fprefix.p; a.block_sums = p->block_sums.p;
     a.nwords = (uint32_t)((C + 31) / 32);
     a.ext_enc = p->ext_enc.p; a.vbase = p->vbase.p; a.lastface = p->lastface.p;
@@ -360,9 +380,14 @@ int vkm_plan_finish(vkm_plan* p, vkm_plan_result* r) {
         if (s.overflow1 || s.overflow2) {
             // optimistic table sizing failed: grow (bounded by 2 slots per corner) and run the import again
             const uint64_t worst = 2ull * p->args.ncorners + 64;
-            if ((uint64_t)p->m1 >= worst || attempt > 8) return fail(VKM_ERR_CAPACITY, "import: hash table overflow at worst-case size");
             CU(cudaStreamSynchronize(p->last_stream));
-            int rc = plan_size_tables(p, std::min<uint64_t>(worst, 2ull * p->m1));
+            int rc = VKM_OK;
+            if (s.overflow1 && p->args.t1_mode == 0 && !s.overflow2) {
+                p->t1_mode = 1;  // the coherent addressing clustered (many triplets per key record): scramble instead
+            } else {
+                if ((uint64_t)p->m1 >= worst || attempt > 12) return fail(VKM_ERR_CAPACITY, "import: hash table overflow at worst-case size");
+                rc = plan_size_tables(p, std::min<uint64_t>(worst, 2ull * p->m1));
+            }
             if (rc) return rc;
             if ((rc = plan_enqueue(p))) return rc;
             continue;
@@ -581,6 +606,7 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
     if (nn) CU(cudaMemcpyAsync(c.nrm.p, nrm, nn * 12, cudaMemcpyHostToDevice, c.st));
     if (nt) CU(cudaMemcpyAsync(c.uv.p, uv, nt * 8, cudaMemcpyHostToDevice, c.st));
     if (C) CU(cudaMemcpyAsync(c.idx.p, idx, C * 12, cudaMemcpyHostToDevice, c.st));
+    c.plan->t1_mode = 0;  // every host call is a new mesh: try the coherent addressing first
     if ((rc = vkm_plan_import(c.plan, c.pos.p, np, c.nrm.p, nn, c.uv.p, nt, c.idx.p, shape_off, nshapes, c.st))) return rc;
     vkm_plan_result r{};
     if ((rc = vkm_plan_finish(c.plan, &r))) return rc;
