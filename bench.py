@@ -32,7 +32,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "mesh triangles/sec (dedup+normals+tangents)"
 UNIT = "triangles/s"
-KERNELS_PER_STEP = 13  # our kernels per import (memset nodes not counted); see vkmesh.cu plan_enqueue
+KERNELS_PER_STEP = 14  # our kernels per import (memset nodes not counted); see vkmesh.cu plan_enqueue
 FALLBACK_HBM_GBS = 6650.0
 
 WORKLOADS = {
@@ -281,8 +281,8 @@ def main():
     names = plan.phase_names()
     # algorithmic bytes each phase is the first to read / the one to write (they sum to B_alg)
     share = {
-        "insert_triplets": 36 * F,                                             # the (v,n,t) index stream
-        "resolve_firsts": mesh.pos.nbytes + mesh.nrm.nbytes + mesh.uv.nbytes + 36,  # attribute arrays + extent
+        "insert_triplets": 36 * F,                                                  # the (v,n,t) index stream
+        "resolve_values": mesh.pos.nbytes + mesh.nrm.nbytes + mesh.uv.nbytes + 36,  # attribute arrays + extent
         "indices": 12 * F,                                                     # u32 index buffer
         "vertices": 48 * U,                                                    # Vertex3D minus tangent
         "tangents": 16 * U,                                                    # tangent column

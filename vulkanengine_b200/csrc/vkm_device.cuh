@@ -6,8 +6,7 @@
 
 namespace vkm {
 
-constexpr uint64_t kEmpty64 = ~0ull;          // empty slot of the (tagged, 64-bit) value table
-constexpr uint32_t kEmpty32 = 0xFFFFFFFFu;     // empty slot of the (32-bit) triplet table
+constexpr uint32_t kEmpty32 = 0xFFFFFFFFu;     // empty slot (both tables hold one u32 per slot)
 constexpr uint32_t kUnmatchable = 0xFFFFFFFFu; // aux marker: key holds NaN/Inf and never matches anything
 constexpr int kMaxProbe = 2048;
 
@@ -39,9 +38,9 @@ struct ImportArgs {
     uint32_t t1_mode;   // 0: locality-preserving home slot (key attribute index * scale), 1: scrambled hash
     uint32_t t1_sel;    // which of v / n / t is the key attribute (the largest attribute array)
     uint32_t t1_scale;  // slots per key-attribute record
-    uint32_t* cand;     // [nwords + 1] bit c set <=> corner c may be the first of its triplet (set by K1)
-    uint64_t* table2;  // value table:   (tag << 32 | first corner)
+    uint32_t* table2;  // value table: (tag << cbits | first corner); 2^cbits > ncorners, so a word is never kEmpty32
     uint32_t m2;
+    uint32_t cbits;    // bits that hold the corner id in a table2 word; the remaining high bits are a hash tag
     uint32_t* slot1;   // [ncorners] slot of every corner in table1
     uint32_t* aux1;    // [m1] per triplet: slot in table2, later the final local vertex index
     uint32_t* fbits;   // [nwords + 1] bit c set <=> corner c creates a vertex

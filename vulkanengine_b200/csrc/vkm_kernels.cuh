@@ -1,9 +1,9 @@
 // sm_100a kernels of the mesh-import path (all HBM/L2-bound integer + gather work; no tensor cores).
 //
-//   k_insert_triplets   A2/A3  read the (v,n,t) index stream with 128-bit loads, hash-insert every corner
-//                              into the triplet table with atomicMin(first corner)          [C-scale]
-//   k_resolve_firsts    A2/A3/A4  first corner of every distinct triplet: gather 8 floats, bounding box,
-//                              NaN/Inf screening, hash-insert the VALUE key into table2      [T-scale work]
+//   k_insert_triplets   A2/A3  read the (v,n,t) index stream with 128-bit loads, insert every corner into the
+//                              triplet table with atomicMin(first corner)                     [C-scale]
+//   k_resolve_slots     A2/A3/A4  per distinct triplet (slot domain): gather 8 floats, bounding box, NaN/Inf
+//                              screening, insert the VALUE key into table2                    [T-scale]
 //   k_mark_unmatchable  A3     NaN/Inf keys: every occurrence creates a vertex (only runs if any seen)
 //   k_mark_value_firsts A3     table2 -> one flag bit per vertex-creating corner
 //   k_scan_*            A3     popcount prefix over the flag bitmap (stable first-occurrence order)
@@ -26,46 +26,19 @@ constexpr int kThreads = 256;
 // K1: triplet insert.  Each thread owns 4 consecutive corners = 48 bytes = three 128-bit loads.
 // The table holds one u32 per slot: the lowest corner id seen so far for the slot's triplet.  Equality
 // is decided exactly, by reading the occupant's own triplet from the index stream (for coherent meshes
-// the occupant is a recent corner, so that read hits L1/L2).  Because corners are visited roughly in
-// order, the occupant is usually already the lowest corner and most duplicates issue no atomic at all.
-// Returns the slot; *cand is set when corner c may be the triplet's first corner.
+// the occupant is a recent corner, so that read hits L1/L2).  The four corners of a thread are inserted
+// one after the other on purpose: corners of one quad repeat triplets, so the later ones hit L1 (a variant
+// that kept four probes in flight per thread measured 1.6x slower on B200: more registers, no reuse).
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t insert_triplet(const ImportArgs& a, uint32_t c, uint32_t v, uint32_t n, uint32_t t,
-                                                   uint32_t sh, uint32_t sh_begin, uint32_t sh_end, bool* cand) {
-    uint32_t s = home_slot(a, v, n, t, sh);
-    for (int probe = 0; probe < kMaxProbe; ++probe) {
-        uint32_t cur = __ldcg(a.table1 + s);
-        if (cur == kEmpty32) {
-            const uint32_t prev = atomicCAS(a.table1 + s, kEmpty32, c);
-            if (prev == kEmpty32) {
-                *cand = true;
-                return s;
-            }
-            cur = prev;
-        }
-        if (cur == c) {
-            *cand = true;
-            return s;
-        }
-        if (cur >= sh_begin && cur < sh_end) {
-            const int32_t* o = a.idx + 3ull * cur;
-            if ((uint32_t)__ldg(o) == v && (uint32_t)__ldg(o + 1) == n && (uint32_t)__ldg(o + 2) == t) {
-                if (cur > c) {
-                    atomicMin(a.table1 + s, c);
-                    *cand = true;
-                }
-                return s;
-            }
-        }
-        s = (s + 1 == a.m1) ? 0 : s + 1;
-    }
-    a.status->overflow1 = 1;
-    return 0;
+__device__ __forceinline__ bool same_triplet(const int32_t* __restrict__ idx, uint32_t occ, uint32_t v, uint32_t n,
+                                             uint32_t t, uint32_t sh_begin, uint32_t sh_end) {
+    if (occ < sh_begin || occ >= sh_end) return false;
+    const int32_t* o = idx + 3ull * occ;
+    return (uint32_t)__ldg(o) == v && (uint32_t)__ldg(o + 1) == n && (uint32_t)__ldg(o + 2) == t;
 }
 
 __global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
-    // whole warps (32 threads = 128 corners = four candidate words) stay in the loop together
-    const uint32_t ngroups = (((a.ncorners + 127) >> 7) << 5);
+    const uint32_t ngroups = (a.ncorners + 3) >> 2;
     for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
         const uint32_t c0 = g << 2;
         int32_t w[12];
@@ -79,14 +52,9 @@ __global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
 #pragma unroll
             for (int i = 0; i < 12; ++i) w[i] = (c0 + i / 3 < a.ncorners) ? __ldg(a.idx + 3ull * c0 + i) : 0;
         }
-        uint32_t sh = 0, sh_begin = 0, sh_end = 0;
-        if (c0 < a.ncorners) {
-            sh = find_shape(a.shape_off, a.nshapes, c0);
-            sh_begin = a.shape_off[sh];
-            sh_end = a.shape_off[sh + 1];
-        }
+        uint32_t sh = find_shape(a.shape_off, a.nshapes, min(c0, a.ncorners - 1));
+        uint32_t sh_begin = a.shape_off[sh], sh_end = a.shape_off[sh + 1];
         uint32_t slots[4];
-        uint32_t nibble = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const uint32_t c = c0 + i;
@@ -97,32 +65,44 @@ __global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
                 sh_begin = a.shape_off[sh];
                 sh_end = a.shape_off[sh + 1];
             }
-            uint32_t v = (uint32_t)w[3 * i], n = (uint32_t)w[3 * i + 1], t = (uint32_t)w[3 * i + 2];
-            if (v >= a.np || n >= a.nn || t >= a.nt) {  // negative ints are huge as unsigned
+            const uint32_t v = (uint32_t)w[3 * i], n = (uint32_t)w[3 * i + 1], t = (uint32_t)w[3 * i + 2];
+            if (v >= a.np || n >= a.nn || t >= a.nt) {
                 a.status->bad_index = 1;
                 continue;
             }
-            bool cand = false;
-            slots[i] = insert_triplet(a, c, v, n, t, sh, sh_begin, sh_end, &cand);
-            nibble |= (cand ? 1u : 0u) << i;
+            uint32_t s = home_slot(a, v, n, t, sh);
+            bool ok = false;
+            for (int probe = 0; probe < kMaxProbe; ++probe) {
+                uint32_t cur = __ldcg(a.table1 + s);
+                if (cur == kEmpty32) {
+                    const uint32_t prev = atomicCAS(a.table1 + s, kEmpty32, c);
+                    if (prev == kEmpty32) { ok = true; break; }
+                    cur = prev;
+                }
+                if (cur == c) { ok = true; break; }
+                if (same_triplet(a.idx, cur, v, n, t, sh_begin, sh_end)) {
+                    if (cur > c) atomicMin(a.table1 + s, c);
+                    ok = true;
+                    break;
+                }
+                s = (s + 1 == a.m1) ? 0 : s + 1;
+            }
+            if (!ok) { a.status->overflow1 = 1; s = 0; }
+            slots[i] = s;
         }
         if (c0 + 4 <= a.ncorners) {
             *reinterpret_cast<uint4*>(a.slot1 + c0) = make_uint4(slots[0], slots[1], slots[2], slots[3]);
         } else {
             for (int i = 0; i < 4 && c0 + i < a.ncorners; ++i) a.slot1[c0 + i] = slots[i];
         }
-        // candidate bitmap: 8 consecutive lanes hold the 32 bits of one word
-        uint32_t word = nibble << ((threadIdx.x & 7) * 4);
-        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 1);
-        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 2);
-        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 4);
-        if ((threadIdx.x & 7) == 0 && (c0 >> 5) < a.nwords) a.cand[c0 >> 5] = word;
     }
 }
 
 // ---------------------------------------------------------------------------------------------
-// K2: first corner of each distinct triplet -> bounding box, NaN/Inf screening, value-key insert.
-// One thread per candidate word (32 corners); only candidates (about one corner in `valence`) do work.
+// Value-level dedup (second level).  Distinct triplets can still carry identical values (duplicated
+// v / vn / vt records), and +0 / -0 must merge, so every distinct triplet inserts its canonical 8-float
+// key into a tagged table with atomicMin(first corner).  Tags only skip gathers: equality is decided
+// exactly on the occupant's own values.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ bool same_value_key(const ImportArgs& a, uint32_t occ, const uint32_t k[8]) {
     const int32_t* o = a.idx + 3ull * occ;
@@ -137,22 +117,22 @@ __device__ __forceinline__ bool same_value_key(const ImportArgs& a, uint32_t occ
 __device__ __forceinline__ uint32_t insert_value(const ImportArgs& a, uint32_t c, const uint32_t k[8], uint32_t sh,
                                                  uint32_t sh_begin, uint32_t sh_end) {
     const uint64_t h = hash_key8(k, sh);
-    const uint32_t tag = (uint32_t)(h >> 32);
-    const uint64_t mine = ((uint64_t)tag << 32) | c;
+    const uint32_t cmask = (a.cbits >= 32) ? 0xFFFFFFFFu : ((1u << a.cbits) - 1u);
+    const uint32_t tag = (a.cbits >= 32) ? 0u : ((uint32_t)(h >> 32) >> a.cbits) << a.cbits;  // high (32 - cbits) bits
+    const uint32_t mine = tag | c;
     uint32_t s = reduce32((uint32_t)h, a.m2);
     for (int probe = 0; probe < kMaxProbe; ++probe) {
-        uint64_t cur = __ldcg(a.table2 + s);
-        if (cur == kEmpty64) {
-            const uint64_t prev = atomicCAS(reinterpret_cast<unsigned long long*>(a.table2 + s), kEmpty64, mine);
-            if (prev == kEmpty64) return s;
+        uint32_t cur = __ldcg(a.table2 + s);
+        if (cur == kEmpty32) {
+            const uint32_t prev = atomicCAS(a.table2 + s, kEmpty32, mine);
+            if (prev == kEmpty32) return s;
             cur = prev;
         }
-        if ((uint32_t)(cur >> 32) == tag) {
-            const uint32_t occ = (uint32_t)cur;
+        if ((cur & ~cmask) == tag) {
+            const uint32_t occ = cur & cmask;
             if (occ == c) return s;
-            // Exact check: tags only skip gathers; a slot only ever holds corners with one canonical value key.
             if (occ >= sh_begin && occ < sh_end && same_value_key(a, occ, k)) {
-                if (occ > c) atomicMin(reinterpret_cast<unsigned long long*>(a.table2 + s), mine);
+                if (occ > c) atomicMin(a.table2 + s, mine);  // same tag: orders by corner
                 return s;
             }
         }
@@ -171,85 +151,64 @@ __device__ __forceinline__ void box_atomics(uint32_t* e, const uint32_t mn[3], c
     }
 }
 
-__global__ void __launch_bounds__(kThreads) k_resolve_firsts(ImportArgs a) {
+// ---------------------------------------------------------------------------------------------
+// K2 (A2 + A4 + second level of A3), slot domain: one thread per triplet-table slot.  An occupied slot
+// is one distinct (shape, v, n, t): gather its 8 floats once, feed the shape's bounding box (the box
+// over distinct triplets equals the box over all corners), screen NaN/Inf, insert the value key.
+// Slot order follows the key attribute's index order, so the gathers are as coherent as the mesh.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_resolve_slots(ImportArgs a) {
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t padded = (a.nwords + 31) & ~31u;  // whole warps stay in the loop (warp reductions below)
-    const uint32_t neutral = 0x80000000u;            // enc_float(+0): the reference's box always contains the origin
-    for (uint32_t w = blockIdx.x * blockDim.x + threadIdx.x; w < padded; w += gridDim.x * blockDim.x) {
+    const uint32_t neutral = 0x80000000u;  // enc_float(+0): the reference's box always contains the origin
+    const uint32_t padded = (a.m1 + 31) & ~31u;  // whole warps stay in the loop (warp reductions below)
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < padded; s += gridDim.x * blockDim.x) {
         uint32_t mn[3] = {neutral, neutral, neutral}, mx[3] = {neutral, neutral, neutral};
-        uint32_t bits = (w < a.nwords) ? a.cand[w] : 0;
-        const uint32_t cbase = w << 5;
-        uint32_t sh = 0, sh_begin = 0, sh_end = 0xFFFFFFFFu;
-        bool word_uniform = true;  // all corners of this word lie in one shape
-        if (w < a.nwords && a.nshapes > 1) {
-            sh = find_shape(a.shape_off, a.nshapes, cbase);
-            sh_begin = a.shape_off[sh];
-            sh_end = a.shape_off[sh + 1];
-            word_uniform = (min(cbase + 31, a.ncorners - 1) < sh_end);
-        } else if (w < a.nwords) {
-            sh_begin = a.shape_off[0];
-            sh_end = a.shape_off[1];
-        }
-        while (bits) {
-            const uint32_t b = __ffs(bits) - 1;
-            bits &= bits - 1;
-            const uint32_t c = cbase + b;
-            const uint32_t s1 = a.slot1[c];
-            if (__ldcg(a.table1 + s1) != c) continue;  // a lower corner took the slot after K1 looked
-            uint32_t csh = sh, cb = sh_begin, ce = sh_end;
-            if (!word_uniform && c >= sh_end) {
-                csh = find_shape(a.shape_off, a.nshapes, c);
-                cb = a.shape_off[csh];
-                ce = a.shape_off[csh + 1];
-            }
+        const uint32_t c = (s < a.m1) ? __ldcs(a.table1 + s) : kEmpty32;
+        const bool occupied = (c != kEmpty32);
+        uint32_t sh = 0xFFFFFFFFu;
+        if (occupied) {
+            // the slot's triplet, read back from its first corner (slot order ~ corner order: coherent gathers)
             const int32_t* o = a.idx + 3ull * c;
+            const uint32_t tv = (uint32_t)__ldg(o), tn = (uint32_t)__ldg(o + 1), tt = (uint32_t)__ldg(o + 2);
+            sh = find_shape(a.shape_off, a.nshapes, c);
             uint32_t k[8];
-            gather_key(a, (uint32_t)__ldg(o), (uint32_t)__ldg(o + 1), (uint32_t)__ldg(o + 2), k);
+            gather_key(a, tv, tn, tt, k);
             bool bad = false;
 #pragma unroll
             for (int i = 0; i < 8; ++i) bad |= nonfinite_bits(k[i]);
-            uint32_t pmn[3] = {neutral, neutral, neutral}, pmx[3] = {neutral, neutral, neutral};
 #pragma unroll
             for (int i = 0; i < 3; ++i) {
                 // strict </> against NaN never updates the reference's box; +-Inf does
-                if ((k[i] & 0x7FFFFFFFu) <= 0x7F800000u) pmn[i] = pmx[i] = enc_float(__uint_as_float(k[i]));
-            }
-            if (word_uniform) {
-#pragma unroll
-                for (int i = 0; i < 3; ++i) {
-                    mn[i] = min(mn[i], pmn[i]);
-                    mx[i] = max(mx[i], pmx[i]);
-                }
-            } else {
-                box_atomics(a.ext_enc + 6u * csh, pmn, pmx);
+                if ((k[i] & 0x7FFFFFFFu) <= 0x7F800000u) mn[i] = mx[i] = enc_float(__uint_as_float(k[i]));
             }
             if (bad) {
-                a.aux1[s1] = kUnmatchable;
+                a.aux1[s] = kUnmatchable;
                 a.status->has_unmatchable = 1;
-                atomicOr(a.fbits + (c >> 5), 1u << (c & 31));
             } else {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) k[i] = canon_bits(k[i]);
-                a.aux1[s1] = insert_value(a, c, k, csh, cb, ce);
+                a.aux1[s] = insert_value(a, c, k, sh, a.shape_off[sh], a.shape_off[sh + 1]);
             }
         }
-        // bounding box: warp-reduce when every lane's word sits inside the same shape, else per-lane atomics
-        const uint32_t sh0 = __shfl_sync(0xFFFFFFFFu, sh, 0);
-        const bool uniform = __all_sync(0xFFFFFFFFu, (sh == sh0 && word_uniform) || w >= a.nwords);
-        if (uniform) {
+        // bounding box: one set of (improvement-checked) atomics per warp when its slots share a shape
+        const uint32_t any = __ballot_sync(0xFFFFFFFFu, occupied);
+        if (any) {
+            const uint32_t sh0 = __shfl_sync(0xFFFFFFFFu, sh, __ffs(any) - 1);
+            if (__all_sync(0xFFFFFFFFu, !occupied || sh == sh0)) {
 #pragma unroll
-            for (int i = 0; i < 3; ++i) {
-                mn[i] = __reduce_min_sync(0xFFFFFFFFu, mn[i]);
-                mx[i] = __reduce_max_sync(0xFFFFFFFFu, mx[i]);
+                for (int i = 0; i < 3; ++i) {
+                    mn[i] = __reduce_min_sync(0xFFFFFFFFu, mn[i]);
+                    mx[i] = __reduce_max_sync(0xFFFFFFFFu, mx[i]);
+                }
+                if (lane == 0) box_atomics(a.ext_enc + 6u * sh0, mn, mx);
+            } else if (occupied) {
+                box_atomics(a.ext_enc + 6u * sh, mn, mx);
             }
-            if (lane == 0) box_atomics(a.ext_enc + 6u * sh0, mn, mx);
-        } else if (w < a.nwords && word_uniform) {
-            box_atomics(a.ext_enc + 6u * sh, mn, mx);
         }
     }
 }
 
-// Every occurrence of a NaN/Inf key creates a vertex (and gets index 0); firsts were flagged in K2.
+// Every occurrence of a NaN/Inf key creates a vertex (and gets index 0).
 __global__ void __launch_bounds__(kThreads) k_mark_unmatchable(ImportArgs a) {
     if (a.status->has_unmatchable == 0) return;
     for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < a.ncorners; c += gridDim.x * blockDim.x) {
@@ -259,9 +218,9 @@ __global__ void __launch_bounds__(kThreads) k_mark_unmatchable(ImportArgs a) {
 
 __global__ void __launch_bounds__(kThreads) k_mark_value_firsts(ImportArgs a) {
     for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < a.m2; s += gridDim.x * blockDim.x) {
-        const uint64_t cur = a.table2[s];
-        if (cur != kEmpty64) {
-            const uint32_t c = (uint32_t)cur;
+        const uint32_t cur = a.table2[s];
+        if (cur != kEmpty32) {
+            const uint32_t c = (a.cbits >= 32) ? cur : (cur & ((1u << a.cbits) - 1u));
             atomicOr(a.fbits + (c >> 5), 1u << (c & 31));
         }
     }
@@ -370,7 +329,8 @@ __global__ void __launch_bounds__(kThreads) k_final_index(ImportArgs a) {
         const uint32_t x = a.aux1[s];
         if (x == kUnmatchable) continue;
         if (x >= a.m2) continue;                      // only after an overflow; the host re-runs then
-        const uint32_t rep = (uint32_t)a.table2[x];  // first corner with this VALUE key
+        const uint32_t word = a.table2[x];
+        const uint32_t rep = (a.cbits >= 32) ? word : (word & ((1u << a.cbits) - 1u));  // first corner with this VALUE key
         if (rep >= a.ncorners) continue;
         const uint32_t sh = find_shape(a.shape_off, a.nshapes, rep);
         a.aux1[s] = rank_of(a, rep) - a.vbase[sh];
@@ -416,25 +376,44 @@ __global__ void __launch_bounds__(kThreads) k_write_indices(ImportArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Vertex records (stable compaction of vertex-creating corners)
+// Vertex records (A2/A8).  Slot domain: the slot whose first corner carries a flag bit writes the 64-byte
+// Vertex3D at the corner's rank.  Slot order ~ corner order for coherent meshes, so the 64-byte records of
+// neighbouring threads land next to each other.  NaN/Inf corners (every occurrence is a vertex) are
+// written by the corner-domain k_write_unmatchable_vertices, which only runs when any exist.
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void store_vertex(float4* dst, const uint32_t k[8]) {
+    // Vertex3D: position @0, normal @12, texcoord @24, color @32 (zero), tangent @48 (filled by the tangent pass)
+    __stcs(dst + 0, make_float4(__uint_as_float(k[0]), __uint_as_float(k[1]), __uint_as_float(k[2]), __uint_as_float(k[3])));
+    __stcs(dst + 1, make_float4(__uint_as_float(k[4]), __uint_as_float(k[5]), __uint_as_float(k[6]), __uint_as_float(k[7])));
+    __stcs(dst + 2, make_float4(0.f, 0.f, 0.f, 0.f));
+    __stcs(dst + 3, make_float4(0.f, 0.f, 0.f, 0.f));
+}
+
 __global__ void __launch_bounds__(kThreads) k_write_vertices(ImportArgs a) {
-    const uint32_t lane = threadIdx.x & 31;
-    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < a.ncorners; c += gridDim.x * blockDim.x) {
-        const uint32_t w = c >> 5;
-        const uint32_t bits = a.fbits[w];
-        if (!((bits >> lane) & 1u)) continue;
-        const uint32_t id = a.fprefix[w] + __popc(bits & ((1u << lane) - 1u));
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < a.m1; s += gridDim.x * blockDim.x) {
+        const uint32_t c = __ldcs(a.table1 + s);
+        if (c == kEmpty32 || c >= a.ncorners) continue;
+        const uint32_t w = c >> 5, bits = a.fbits[w];
+        if (!((bits >> (c & 31)) & 1u)) continue;  // a value duplicate of an earlier triplet
+        const uint32_t id = a.fprefix[w] + __popc(bits & ((1u << (c & 31)) - 1u));
         if (id >= a.vertex_capacity) continue;
         const int32_t* o = a.idx + 3ull * c;
         uint32_t k[8];
         gather_key(a, (uint32_t)__ldg(o), (uint32_t)__ldg(o + 1), (uint32_t)__ldg(o + 2), k);
-        float4* dst = a.out_vtx + 4ull * id;
-        // Vertex3D: position @0, normal @12, texcoord @24, color @32 (zero), tangent @48 (filled by k_tangents)
-        dst[0] = make_float4(__uint_as_float(k[0]), __uint_as_float(k[1]), __uint_as_float(k[2]), __uint_as_float(k[3]));
-        dst[1] = make_float4(__uint_as_float(k[4]), __uint_as_float(k[5]), __uint_as_float(k[6]), __uint_as_float(k[7]));
-        dst[2] = make_float4(0.f, 0.f, 0.f, 0.f);
-        dst[3] = make_float4(0.f, 0.f, 0.f, 0.f);
+        store_vertex(a.out_vtx + 4ull * id, k);
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_write_unmatchable_vertices(ImportArgs a) {
+    if (a.status->has_unmatchable == 0) return;
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < a.ncorners; c += gridDim.x * blockDim.x) {
+        if (a.aux1[a.slot1[c]] != kUnmatchable) continue;
+        const uint32_t id = rank_of(a, c);
+        if (id >= a.vertex_capacity) continue;
+        const int32_t* o = a.idx + 3ull * c;
+        uint32_t k[8];
+        gather_key(a, (uint32_t)__ldg(o), (uint32_t)__ldg(o + 1), (uint32_t)__ldg(o + 2), k);
+        store_vertex(a.out_vtx + 4ull * id, k);
     }
 }
 

@@ -85,8 +85,8 @@ struct DevBuf {
     }
 };
 
-enum Phase { PH_CLEAR = 0, PH_INSERT, PH_FIRSTS, PH_SCAN, PH_INDICES, PH_VERTICES, PH_TANGENTS, PH_COUNT };
-const char* kPhaseNames[PH_COUNT] = {"clear", "insert_triplets", "resolve_firsts", "mark_scan", "indices",
+enum Phase { PH_CLEAR = 0, PH_INSERT, PH_VALUES, PH_SCAN, PH_INDICES, PH_VERTICES, PH_TANGENTS, PH_COUNT };
+const char* kPhaseNames[PH_COUNT] = {"clear", "insert_triplets", "resolve_values", "mark_scan", "indices",
                                      "vertices", "tangents"};
 
 }  // namespace
@@ -97,9 +97,8 @@ struct vkm_plan {
     cudaStream_t last_stream = nullptr;
     uint32_t m1 = 0, m2 = 0;       // allocated slots
     uint32_t t1_mode = 0;          // sticky: 0 = locality-preserving triplet table, 1 = scrambled (after clustering)
-    DevBuf<uint32_t> table1;
-    DevBuf<uint64_t> table2;
-    DevBuf<uint32_t> cand, slot1, aux1, fbits, fprefix, block_sums, ext_enc, vbase, lastface, out_idx, shape_off;
+    DevBuf<uint32_t> table1, table2;
+    DevBuf<uint32_t> slot1, aux1, fbits, fprefix, block_sums, ext_enc, vbase, lastface, out_idx, shape_off;
     DevBuf<float4> out_vtx;
     DevBuf<Status> status;
     // pinned host mirrors
@@ -169,6 +168,8 @@ int plan_enqueue(vkm_plan* p) {
     a.table2 = p->table2.p;
     a.aux1 = p->aux1.p;
     a.m2 = p->m2;
+    a.cbits = 1;
+    while (a.cbits < 32 && (1ull << a.cbits) <= (uint64_t)a.ncorners) a.cbits++;  // 2^cbits > ncorners
     {
         // Triplet table addressing.  Mode 0: home slot = (index into the largest attribute array) * scale, which
         // keeps the table access pattern as coherent as the mesh's own index order.  Needs scale slots per record.
@@ -190,7 +191,7 @@ int plan_enqueue(vkm_plan* p) {
     if (T) CU(cudaEventRecord(ev[PH_CLEAR], st));
     CU(cudaMemsetAsync(p->status.p, 0, sizeof(Status), st));
     CU(cudaMemsetAsync(a.table1, 0xFF, (uint64_t)a.m1 * 4, st));
-    CU(cudaMemsetAsync(a.table2, 0xFF, (uint64_t)a.m2 * 8, st));
+    CU(cudaMemsetAsync(a.table2, 0xFF, (uint64_t)a.m2 * 4, st));
     CU(cudaMemsetAsync(a.fbits, 0, ((uint64_t)a.nwords + 1) * 4, st));
     // encoded +0.0 everywhere: GeometryExtent extent{} (mesh_loader.cpp:230)
     CU(cudaMemsetAsync(a.ext_enc, 0, (uint64_t)a.nshapes * 6 * 4, st));
@@ -201,10 +202,10 @@ int plan_enqueue(vkm_plan* p) {
     }
     if (T) CU(cudaEventRecord(ev[PH_INSERT], st));
     k_insert_triplets<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
-    if (T) CU(cudaEventRecord(ev[PH_FIRSTS], st));
-    k_resolve_firsts<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
-    k_mark_unmatchable<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
+    if (T) CU(cudaEventRecord(ev[PH_VALUES], st));
+    k_resolve_slots<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_SCAN], st));
+    k_mark_unmatchable<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
     k_mark_value_firsts<<<grid_for(a.m2, kThreads, dev), kThreads, 0, st>>>(a);
     const uint32_t ntiles = std::max<uint32_t>(1, (a.nwords + kScanTile - 1) / kScanTile);
     k_scan_tiles<<<ntiles, kScanThreads, 0, st>>>(a);
@@ -216,7 +217,8 @@ int plan_enqueue(vkm_plan* p) {
     k_final_index<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
     k_write_indices<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_VERTICES], st));
-    k_write_vertices<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
+    k_write_vertices<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
+    k_write_unmatchable_vertices<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_TANGENTS], st));
     k_per_vertex_frames<0><<<grid_for(a.vertex_capacity, kThreads, dev), kThreads, 0, st>>>(
         a.out_vtx, a.out_idx, a.lastface, &p->status.p->total_vertices, a.vertex_capacity, a.shape_off, a.vbase,
@@ -270,7 +272,6 @@ int vkm_plan_create(const vkm_plan_desc* desc, vkm_plan** out) {
     auto chk = [&](int r) { if (rc == VKM_OK) rc = r; };
     chk(plan_size_tables(p, initial_slots(p->desc)));
     chk(p->slot1.ensure(C + 4));
-    chk(p->cand.ensure(W + 4));
     chk(p->fbits.ensure(W + 1));
     chk(p->fprefix.ensure(W + 1));
     chk(p->block_sums.ensure((W + kScanTile - 1) / kScanTile + 1));
@@ -306,7 +307,7 @@ void vkm_plan_destroy(vkm_plan* p) {
     if (!p) return;
     cudaSetDevice(p->desc.device);
     if (p->pending && p->done) cudaEventSynchronize(p->done);
-    p->table1.release(); p->table2.release(); p->cand.release(); p->slot1.release(); p->aux1.release(); p->fbits.release();
+    p->table1.release(); p->table2.release(); p->slot1.release(); p->aux1.release(); p->fbits.release();
     p->fprefix.release(); p->block_sums.release(); p->ext_enc.release(); p->vbase.release(); p->lastface.release();
     p->out_idx.release(); p->shape_off.release(); p->out_vtx.release(); p->status.release();
     if (p->h_status) cudaFreeHost(p->h_status);
@@ -357,7 +358,6 @@ int vkm_plan_import(vkm_plan* p, const float* d_pos, uint64_t np, const float* d
     a.ncorners = (uint32_t)C;
     a.shape_off = p->shape_off.p;
     a.nshapes = nshapes;
-    a.cand = p->cand.p;
     a.slot1 = p->slot1.p; a.fbits = p->fbits.p; a.fprefix = p->fprefix.p; a.block_sums = p->block_sums.p;
     a.nwords = (uint32_t)((C + 31) / 32);
     a.ext_enc = p->ext_enc.p; a.vbase = p->vbase.p; a.lastface = p->lastface.p;
