@@ -144,6 +144,28 @@ int vkm_generate_tangents_dev(uint32_t vertex_count, void* d_vertices, uint32_t 
 int vkm_generate_normals_dev(uint32_t vertex_count, void* d_vertices, uint32_t index_count,
                              const uint32_t* d_indices, uint32_t* d_scratch, void* stream);
 
+/* Tangent generation for callers that must not allocate device memory.  (This entry point has no counterpart in
+ * the reference; it exists only because of how this library is deployed.)
+ *
+ * Who needs it: code that runs while the renderer is drawing -- a hot-reload hook, a procedural-geometry update
+ * inside the frame loop -- where a cudaMalloc/cudaFree would synchronise the whole device and stall the frames in
+ * flight, and engines that hand all remaining device memory to their own allocator at start-up, so that a later
+ * cudaMalloc can simply fail.  Such a caller owns `d_vertices` and `d_indices` but has nowhere to put the
+ * per-vertex "last triangle" words that vkm_generate_tangents_dev takes as `d_scratch`.
+ *
+ * Here that scratch is a fixed array inside the library's device image: VKM_NOALLOC_MAX_VERTICES words (4 MiB),
+ * resident on every GPU that loads the library until the process exits.  The call makes no cudaMalloc/cudaFree
+ * and uses no allocating library routine.  Same results as vkm_generate_tangents_dev, asynchronous on `stream`.
+ *   - vertex_count > VKM_NOALLOC_MAX_VERTICES is rejected with VKM_ERR_CAPACITY (nothing is launched).
+ *   - The first call on each device looks the array's device address up (once per device, with that device
+ *     current).  Make that first call during set-up, before any stream capture begins.
+ *   - All calls on a device share the one array and it keeps whatever the previous call left; every call first
+ *     zeroes the words it is going to use.  Two calls whose GPU work overlaps (different streams, or different
+ *     host threads on the same device) race on the array: serialise them. */
+#define VKM_NOALLOC_MAX_VERTICES (1u << 20)
+int vkm_generate_tangents_dev_noalloc(uint32_t vertex_count, void* d_vertices, uint32_t index_count,
+                                      const uint32_t* d_indices, void* stream);
+
 /* Thin device-memory helpers so that non-CUDA callers (ctypes, the bench) need no second runtime. */
 int vkm_dev_alloc(int device, uint64_t bytes, void** d_ptr);
 int vkm_dev_free(int device, void* d_ptr);

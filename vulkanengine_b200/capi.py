@@ -29,6 +29,7 @@ SYMBOLS = [
     "vkm_import_shapes", "vkm_free_shape", "vkm_host_alloc", "vkm_host_free",
     "vkm_plan_create", "vkm_plan_destroy", "vkm_plan_import", "vkm_plan_finish", "vkm_plan_set_timing",
     "vkm_plan_phase_name", "vkm_generate_tangents_dev", "vkm_generate_normals_dev",
+    "vkm_generate_tangents_dev_noalloc",
     "vkm_dev_alloc", "vkm_dev_free", "vkm_dev_upload", "vkm_dev_download", "vkm_dev_sync",
 ]
 
@@ -106,6 +107,8 @@ def lib():
     for fn in (L.vkm_generate_tangents_dev, L.vkm_generate_normals_dev):
         fn.restype = C.c_int
         fn.argtypes = [C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.vkm_generate_tangents_dev_noalloc.restype = C.c_int
+    L.vkm_generate_tangents_dev_noalloc.argtypes = [C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
     L.vkm_dev_alloc.restype = C.c_int
     L.vkm_dev_alloc.argtypes = [C.c_int, C.c_uint64, C.POINTER(C.c_void_p)]
     L.vkm_dev_free.argtypes = [C.c_int, C.c_void_p]

@@ -467,6 +467,59 @@ int vkm_generate_normals_dev(uint32_t vc, void* d_v, uint32_t ic, const uint32_t
 }
 
 // ------------------------------------------------------------------------------------------------
+// Tangents without any device allocation (see the header for who needs this and why).
+//
+// The per-vertex "last triangle" words live in a file-scope device array instead of caller scratch.  In host
+// code the name `g_noalloc_scratch` is only a handle for the symbol, not something a kernel can dereference:
+// the real device address differs per GPU and has to be asked for with cudaGetSymbolAddress while that GPU is
+// current.  That lookup happens once per device (first call) and the address is cached below.
+// Layout: [0, VKM_NOALLOC_MAX_VERTICES) last-triangle words, then one word that collects the
+// "index out of range" flag (ignored, like the sink of vkm_generate_tangents_dev).
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) uint32_t g_noalloc_scratch[VKM_NOALLOC_MAX_VERTICES + 64];
+
+namespace {
+std::mutex g_noalloc_mu;
+uint32_t* g_noalloc_addr[64] = {nullptr};  // device address of g_noalloc_scratch, per CUDA ordinal
+}  // namespace
+
+int vkm_generate_tangents_dev_noalloc(uint32_t vertex_count, void* d_vertices, uint32_t index_count,
+                                      const uint32_t* d_indices, void* stream) {
+    if (vkm_device_count() == 0) return fail(VKM_ERR_NO_DEVICE, "no CUDA device (there is no CPU path)");
+    if (vertex_count > VKM_NOALLOC_MAX_VERTICES)
+        return fail(VKM_ERR_CAPACITY,
+                    "vkm_generate_tangents_dev_noalloc: %u vertices exceed the built-in scratch (%u); use "
+                    "vkm_generate_tangents_dev with caller scratch",
+                    vertex_count, VKM_NOALLOC_MAX_VERTICES);
+    if (vertex_count == 0 || index_count < 3) return VKM_OK;
+    if (!d_vertices || !d_indices) return fail(VKM_ERR_INVALID_ARG, "vkm_generate_tangents_dev_noalloc: null buffer");
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(VKM_ERR_INVALID_ARG, "vkm_generate_tangents_dev_noalloc: device ordinal %d", dev);
+    uint32_t* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_addr[dev]) {  // first call on this device: resolve the symbol for the current device
+            uint32_t* p = nullptr;
+            CU(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+            g_noalloc_addr[dev] = p;
+        }
+        scratch = g_noalloc_addr[dev];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    uint32_t* flag = scratch + VKM_NOALLOC_MAX_VERTICES;
+    // The array still holds the previous call's words: zero exactly what this call reads.
+    CU(cudaMemsetAsync(scratch, 0, (uint64_t)vertex_count * 4, st));
+    CU(cudaMemsetAsync(flag, 0, 4, st));
+    k_last_face<<<grid_for(index_count / 3, kThreads, dev), kThreads, 0, st>>>(d_indices, index_count, vertex_count,
+                                                                             scratch, flag);
+    k_per_vertex_frames<0><<<grid_for(vertex_count, kThreads, dev), kThreads, 0, st>>>(
+        (float4*)d_vertices, d_indices, scratch, nullptr, vertex_count, nullptr, nullptr, 1, vertex_count);
+    CU(cudaGetLastError());
+    return VKM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // Host entry points
 // ------------------------------------------------------------------------------------------------
 namespace {
