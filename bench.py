@@ -41,6 +41,8 @@ WORKLOADS = {
     "grid1m": (708, None, "synthetic 1.0M-triangle grid mesh, configs[1]"),
     "highdup16m_perm": (2896, 0x5EED0003, "16.8M-triangle grid, seeded random face order (locality defeated)"),
     "grid64m": (5793, None, "67.1M-triangle grid (configs[4] base, without injections)"),
+    # strong scaling: a FIXED batch of independent meshes, LPT-partitioned over the ranks (configs[3])
+    "batch10k": (None, None, "batch of 10k synthetic meshes (1k-100k triangles each, log-uniform), configs[3]"),
 }
 
 
@@ -182,6 +184,7 @@ def main():
     ap.add_argument("--workload", default="highdup16m", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--batch-meshes", type=int, default=10000, help="mesh count of the batch10k workload")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -233,13 +236,25 @@ def main():
         return float(t.item())
 
     n, perm, desc = WORKLOADS[args.workload]
-    # independent meshes per rank: same shape family, different placement
-    mesh = synth.grid(n, permute_seed=perm, offset=(float(rank), -float(rank), 0.5 * rank), scale=1.0 + 0.25 * rank)
+    scaling = "weak"
+    if args.workload == "batch10k":
+        from vulkanengine_b200 import sharding
+
+        scaling = "strong"
+        ns, tris = sharding.batch_sizes(args.batch_meshes)
+        parts = sharding.lpt_partition(tris, world)
+        mesh = sharding.build_shard(ns, parts[rank])
+        desc += f"; {args.batch_meshes} meshes, LPT partition, imbalance {sharding.imbalance(tris, parts):.4f}"
+    else:
+        # independent meshes per rank: same shape family, different placement
+        mesh = synth.grid(n, permute_seed=perm, offset=(float(rank), -float(rank), 0.5 * rank), scale=1.0 + 0.25 * rank)
+    nshapes = len(mesh.shape_offsets) - 1
     F, C = mesh.triangles, mesh.corners
     max_attrib = max(len(mesh.pos), len(mesh.nrm), len(mesh.uv))
 
     d_pos, d_nrm, d_uv, d_idx = (capi.DeviceArray(dev, a) for a in (mesh.pos, mesh.nrm, mesh.uv, mesh.idx))
-    plan = capi.Plan(dev, C, max_attrib=max_attrib, max_vertices=max_attrib + max_attrib // 8 + 1024, max_shapes=1)
+    plan = capi.Plan(dev, C, max_attrib=max_attrib, max_vertices=max_attrib + max_attrib // 8 + 1024,
+                     max_shapes=nshapes)
     stream = torch.cuda.Stream(device=dev)
 
     def step():
@@ -325,15 +340,17 @@ def main():
 
     h_pos, h_nrm, h_uv, h_idx = (pinned_copy(a) for a in (mesh.pos, mesh.nrm, mesh.uv, mesh.idx))
     so = np.ascontiguousarray(mesh.shape_offsets, np.uint64)
-    out = (capi.ShapeOut * 1)()
+    out = (capi.ShapeOut * nshapes)()
 
     def e2e_step():
         rc = L.vkm_import_shapes(h_pos, len(mesh.pos), h_nrm, len(mesh.nrm), h_uv, len(mesh.uv), h_idx, so.ctypes.data,
-                                 1, out)
+                                 nshapes, out)
         if rc:
             raise SystemExit("vkm_import_shapes failed: " + L.vkm_last_error().decode())
-        nv, ni = out[0].vertex_count, out[0].index_count
-        L.vkm_free_shape(C_.byref(out[0]))
+        nv = sum(out[i].vertex_count for i in range(nshapes))
+        ni = sum(out[i].index_count for i in range(nshapes))
+        for i in range(nshapes):
+            L.vkm_free_shape(C_.byref(out[i]))
         return nv, ni
 
     capi.init([dev])
@@ -365,10 +382,11 @@ def main():
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "u32+f32", "data": "synthetic",
             "config": {"workload": args.workload, "description": desc, "triangles_per_gpu": F, "corners_per_gpu": C,
-                       "unique_vertices_per_gpu": U, "meshes_per_gpu": 1, "parallelism": f"{world} independent mesh(es), one per GPU, no collective",
+                       "unique_vertices_per_gpu": U, "meshes_per_gpu": nshapes,
+                       "parallelism": f"{world} rank(s), independent meshes sharded over GPUs, no collective",
                        "l2": f"inputs {mesh.input_bytes() / 1e6:.0f} MB + outputs {(64 * U + 4 * C) / 1e6:.0f} MB per step exceed the 126 MB L2 (no flush needed)"
                              if mesh.input_bytes() > 200e6 else "working set below L2 size: numbers are L2-warm"},
             "roofline": roofline, "pipeline_roofline": pipeline_roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,

@@ -200,6 +200,18 @@ def test_plan_device_resident_matches_host_entry():
     plan.destroy()
 
 
+def test_sharded_batch_driver_matches_oracle():
+    """The multi-GPU host logic (vulkanengine_b200/sharding.py) over the CUDA path, both shards on this GPU."""
+    from vulkanengine_b200 import sharding
+
+    ns, _ = sharding.batch_sizes(30, min_tris=50, max_tris=6000)
+    want = sharding.run_sharded(ns, 0, 1, port.import_arrays)
+    got = {}
+    for rank in range(2):
+        got.update(sharding.run_sharded(ns, rank, 2, capi.import_shapes, gather_fn=lambda o: [o]))
+    assert got == want
+
+
 # ---------------------------------------------------------------- full-size property checks (no oracle run)
 def test_config3_16m_properties():
     """16.7M-triangle high-duplication grid: too slow for the CPU oracle inside the test budget, so check
@@ -233,3 +245,84 @@ def test_config3_16m_properties():
     complete = (n + 1) * (rows - 1)  # vertices whose every incident triangle lies in the slice
     ok, msg = vertices_equal(sub[:complete], out.vertices[:complete])
     assert ok, msg
+
+
+def _check_import_properties(m, out, sample=2_000_000, seed=1):
+    """Size-independent proof obligations that pin the result uniquely (for one shape):
+       (a) every finite corner's vertex carries exactly the corner's expanded values (canonical -0 -> +0);
+           every NaN/Inf corner wrote index 0 and created its own vertex with its own bits;
+       (b) no two vertices referenced by finite corners are canonically equal (nothing left unmerged);
+       (c) vertices are numbered in order of creation (first occurrence order)."""
+    idx, vtx = out.indices, out.vertices
+    C = m.corners
+    U = len(vtx)
+    pos, nrm, uv = m.pos[m.idx[:, 0]], None, None  # positions of all corners (cheap: 12 B each)
+    finite = np.isfinite(pos).all(1)
+    del pos
+    finite &= np.isfinite(m.nrm[:, :][m.idx[:, 1]]).all(1)
+    finite &= np.isfinite(m.uv[m.idx[:, 2]]).all(1)
+    nonfinite_pos = np.nonzero(~finite)[0]
+    assert np.all(idx[nonfinite_pos] == 0)
+
+    def canon(a):
+        b = a.view(np.uint32).copy()
+        b[b == 0x80000000] = 0
+        return b
+
+    # (a) on a sample of finite corners
+    rng = np.random.default_rng(seed)
+    fin_pos = np.nonzero(finite)[0]
+    c = fin_pos[rng.integers(0, len(fin_pos), min(sample, len(fin_pos)))]
+    v = vtx[idx[c]]
+    assert np.array_equal(canon(v["position"]), canon(m.pos[m.idx[c, 0]]))
+    assert np.array_equal(canon(v["normal"]), canon(m.nrm[m.idx[c, 1]]))
+    assert np.array_equal(canon(v["texcoord"]), canon(m.uv[m.idx[c, 2]]))
+    assert not vtx["color"].any()
+    # (c) creation order
+    creation = np.full(U, C, dtype=np.int64)
+    creation[idx[fin_pos][::-1]] = fin_pos[::-1]  # last write wins -> smallest corner per vertex id
+    unref = np.nonzero(creation == C)[0]          # vertices no finite corner references = NaN/Inf-created
+    assert len(unref) == len(nonfinite_pos), (len(unref), len(nonfinite_pos))
+    creation[unref] = nonfinite_pos
+    assert np.all(np.diff(creation) > 0)
+    # NaN/Inf-created vertices carry their corner's own bits
+    if len(unref):
+        vb = vtx[unref]
+        a = vb["position"].view(np.uint32)
+        b = m.pos[m.idx[nonfinite_pos, 0]].view(np.uint32)
+        assert np.all((a == b) | (np.isnan(vb["position"]) & np.isnan(m.pos[m.idx[nonfinite_pos, 0]])))
+    # the stored vertex keeps the FIRST-SEEN bit pattern (e.g. which of +0 / -0 arrived first), not a canonical one
+    ids = rng.integers(0, U, min(200_000, U))
+    ids = ids[creation[ids] < C]
+    cc = creation[ids]
+    nanok = lambda a, b: np.all((a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b)))
+    assert nanok(vtx["position"][ids], m.pos[m.idx[cc, 0]])
+    assert nanok(vtx["normal"][ids], m.nrm[m.idx[cc, 1]])
+    assert nanok(vtx["texcoord"][ids], m.uv[m.idx[cc, 2]])
+    # (b) uniqueness of canonical keys among finite-referenced vertices (64-bit mix of the 8 words)
+    ref = np.ones(U, bool)
+    ref[unref] = False
+    k = canon(np.ascontiguousarray(vtx.view(np.uint32).reshape(-1, 16)[:, :8][ref])).astype(np.uint64)
+    h = np.zeros(len(k), np.uint64)
+    for j in range(8):
+        h = (h ^ k[:, j]) * np.uint64(0x9E3779B97F4A7C15)
+        h ^= h >> np.uint64(29)
+    assert len(np.unique(h)) == len(h)
+
+
+def test_properties_hold_on_medium_adversarial_and_match_oracle():
+    m = synth.adversarial(700, frac=2e-3, nan_frac=1e-3)  # ~1M triangles
+    out = gpu_of(m)[0]
+    _check_import_properties(m, out, sample=500_000)
+    assert_shapes_equal([out], oracle_of(m))
+
+
+@pytest.mark.skipif(__import__("os").environ.get("VKM_SKIP_HUGE") == "1", reason="VKM_SKIP_HUGE=1")
+def test_config5_adversarial_64m_properties():
+    """67M-triangle adversarial mesh (degenerate triangles, duplicated records, +-0 twins, 1-ulp twins, NaN):
+    the CPU oracle would need minutes, so the result is pinned by the property set above."""
+    m = synth.adversarial(5793, frac=2e-4, nan_frac=2e-5)
+    assert m.triangles > 67_000_000
+    out = gpu_of(m)[0]
+    assert len(out.vertices) < (1 << 26)  # the reference's own u32 byte-size limit (mesh_loader.cpp:301)
+    _check_import_properties(m, out, sample=3_000_000)
