@@ -180,6 +180,48 @@ def test_generate_tangents_out_of_range_index_is_an_error():
     assert e.value.code == 2
 
 
+def _dedup_case(rng, n, kind):
+    v = np.zeros(n, capi.VERTEX_DTYPE)
+    f = v.view(np.float32).reshape(n, 16)
+    if kind == "exact":      # many exact duplicates, all 16 floats live
+        base = rng.standard_normal((max(4, n // 5), 16)).astype(np.float32)
+        f[:] = base[rng.integers(0, len(base), n)]
+    elif kind == "epsilon":  # values on a 4e-8 lattice: chains A~B~C with A!~C (non-transitive epsilon equality)
+        f[:, :3] = (rng.integers(0, 12, (n, 3)) * np.float32(4e-8)).astype(np.float32)
+        f[:, 6] = rng.integers(0, 2, n)
+    elif kind == "mixed":    # big coordinates (exact-only regime), +-0, NaN and Inf rows, epsilon-close small ones
+        f[:, :3] = rng.integers(-3, 4, (n, 3)).astype(np.float32) * np.float32(1500.0)
+        f[: n // 3, 0] = (rng.integers(0, 6, n // 3) * np.float32(5e-8)).astype(np.float32)
+        f[rng.integers(0, n, n // 10), 1] = -0.0
+        f[rng.integers(0, n, max(1, n // 20)), 2] = np.nan
+        f[rng.integers(0, n, max(1, n // 20)), 0] = np.inf
+        f[:, 12:16] = rng.integers(0, 2, (n, 4))
+    idx = rng.integers(0, n, 3 * n).astype(np.uint32)
+    return v, idx
+
+
+@pytest.mark.parametrize("kind,n", [("exact", 300), ("epsilon", 400), ("mixed", 500), ("exact", 20000), ("epsilon", 5000)])
+def test_deduplicate_vertices_literal_semantics_match_oracle(kind, n):
+    rng = np.random.default_rng(n)
+    v, idx = _dedup_case(rng, n, kind)
+    want_v, want_i = port.deduplicate_vertices(v.view(VERTEX_DTYPE), idx)
+    got_v, got_i = capi.deduplicate_vertices(v, idx)
+    assert len(got_v) == len(want_v) and len(want_v) < n
+    assert np.array_equal(got_i, want_i)
+    ok, msg = vertices_equal(got_v, want_v)
+    assert ok, msg
+
+
+def test_deduplicate_vertices_edge_cases():
+    v = np.zeros(0, capi.VERTEX_DTYPE)
+    gv, gi = capi.deduplicate_vertices(v, np.zeros(0, np.uint32))
+    assert len(gv) == 0 and len(gi) == 0
+    v = np.zeros(3, capi.VERTEX_DTYPE)  # three identical vertices, an index beyond the array
+    gv, gi = capi.deduplicate_vertices(v, np.array([0, 1, 2, 7], np.uint32))
+    wv, wi = port.deduplicate_vertices(v.view(VERTEX_DTYPE), np.array([0, 1, 2, 7], np.uint32))
+    assert len(gv) == len(wv) == 1 and np.array_equal(gi, wi)
+
+
 # ---------------------------------------------------------------- device-resident plan API
 def test_plan_device_resident_matches_host_entry():
     m = synth.concat([synth.grid(64), synth.uv_sphere(12, 24), synth.adversarial(32)])

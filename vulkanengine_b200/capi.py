@@ -189,7 +189,9 @@ def deduplicate_vertices(vertices: np.ndarray, indices: np.ndarray):
     if n == 0xFFFFFFFF:
         raise VkmError(-1, lib().vkm_last_error().decode())
     v = _copy_out(out.value, 64 * n, VERTEX_DTYPE)
-    C.CDLL(None).free(out)
+    libc = C.CDLL(None)
+    libc.free.argtypes = [C.c_void_p]
+    libc.free(out)  # malloc()ed by the library, as the reference's Platform::AllocMemory result is
     return v, idx
 
 

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "vkm_kernels.cuh"
+#include "vkm_dedup_util.cuh"
 
 using namespace vkm;
 
@@ -610,9 +611,65 @@ void vkm_shutdown(void) {
 int vkm_generate_tangents(uint32_t vc, void* v, uint32_t ic, const uint32_t* idx) { return frames_host(0, vc, v, ic, idx); }
 int vkm_generate_normals(uint32_t vc, void* v, uint32_t ic, const uint32_t* idx) { return frames_host(1, vc, v, ic, idx); }
 
-uint32_t vkm_deduplicate_vertices(uint32_t, const void*, uint32_t, uint32_t*, void**) {
-    fail(VKM_ERR_INVALID_ARG, "vkm_deduplicate_vertices: not built yet");
-    return 0xFFFFFFFFu;
+static int dedup_host(uint32_t vc, const void* vertices, uint32_t ic, uint32_t* indices, void** out_vertices,
+                      uint32_t* out_count) {
+    if (!out_vertices || (vc && !vertices) || (ic && !indices)) return fail(VKM_ERR_INVALID_ARG, "vkm_deduplicate_vertices: null argument");
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    HostCtx& c = g_ctx;
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    *out_count = 0;
+    if (vc == 0) {
+        *out_vertices = malloc(1);
+        return *out_vertices ? VKM_OK : fail(VKM_ERR_OOM, "host allocation failed");
+    }
+    uint32_t buckets = 1024;
+    while (buckets < 2ull * vc && buckets < (1u << 30)) buckets <<= 1;
+    DevBuf<float4> out;
+    DevBuf<uint32_t> head, next, m, rf, cnt;
+    auto cleanup = [&]() { out.release(); head.release(); next.release(); m.release(); rf.release(); cnt.release(); };
+    if ((rc = c.vtx.ensure((uint64_t)vc * 4)) || (rc = c.ind.ensure(std::max<uint32_t>(ic, 1))) ||
+        (rc = out.ensure((uint64_t)vc * 4)) || (rc = head.ensure(buckets)) || (rc = next.ensure(vc)) ||
+        (rc = m.ensure(vc)) || (rc = rf.ensure(vc)) || (rc = cnt.ensure(1))) {
+        cleanup();
+        return rc;
+    }
+    const int dev = c.devices[0];
+    cudaError_t e = cudaSuccess;
+    auto cu = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+    cu(cudaMemcpyAsync(c.vtx.p, vertices, (uint64_t)vc * 64, cudaMemcpyHostToDevice, c.st));
+    if (ic) cu(cudaMemcpyAsync(c.ind.p, indices, (uint64_t)ic * 4, cudaMemcpyHostToDevice, c.st));
+    cu(cudaMemsetAsync(head.p, 0xFF, (uint64_t)buckets * 4, c.st));
+    k_dd_build<<<grid_for(vc, kThreads, dev), kThreads, 0, c.st>>>(c.vtx.p, vc, head.p, next.p, buckets - 1);
+    k_dd_match<<<grid_for(vc, kThreads, dev), kThreads, 0, c.st>>>(c.vtx.p, vc, head.p, next.p, buckets - 1, m.p);
+    k_dd_sequence<<<1, 32, 0, c.st>>>(m.p, vc, rf.p, cnt.p);
+    k_dd_emit<<<grid_for(vc, kThreads, dev), kThreads, 0, c.st>>>(c.vtx.p, vc, rf.p, out.p);
+    if (ic) k_dd_remap<<<grid_for(ic, kThreads, dev), kThreads, 0, c.st>>>(c.ind.p, ic, vc, rf.p, m.p, cnt.p);
+    cu(cudaGetLastError());
+    uint32_t n = 0;
+    cu(cudaMemcpyAsync(&n, cnt.p, 4, cudaMemcpyDeviceToHost, c.st));
+    cu(cudaStreamSynchronize(c.st));
+    if (e == cudaSuccess) {
+        // Platform::AllocMemory == malloc (platform_Win32.cpp:367-369): the caller frees with free()
+        *out_vertices = malloc(std::max<uint64_t>((uint64_t)n * 64, 1));
+        if (!*out_vertices) {
+            cleanup();
+            return fail(VKM_ERR_OOM, "host allocation failed");
+        }
+        if (n) cu(cudaMemcpyAsync(*out_vertices, out.p, (uint64_t)n * 64, cudaMemcpyDeviceToHost, c.st));
+        if (ic) cu(cudaMemcpyAsync(indices, c.ind.p, (uint64_t)ic * 4, cudaMemcpyDeviceToHost, c.st));
+        cu(cudaStreamSynchronize(c.st));
+    }
+    cleanup();
+    if (e != cudaSuccess) return fail(VKM_ERR_CUDA, "vkm_deduplicate_vertices: %s", cudaGetErrorString(e));
+    *out_count = n;
+    return VKM_OK;
+}
+
+uint32_t vkm_deduplicate_vertices(uint32_t vc, const void* vertices, uint32_t ic, uint32_t* indices, void** out_vertices) {
+    uint32_t n = 0;
+    if (dedup_host(vc, vertices, ic, indices, out_vertices, &n) != VKM_OK) return 0xFFFFFFFFu;
+    return n;
 }
 
 void vkm_free_shape(vkm_shape_out* s) {
