@@ -213,6 +213,7 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = local_rank
     if world > 1:
+        os.environ["NCCL_DEBUG"] = os.environ.get("VKM_NCCL_DEBUG", "WARN")  # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():

@@ -94,6 +94,20 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
                       vkm_shape_out* out);
 void vkm_free_shape(vkm_shape_out* shape);
 
+/* ---- E3DM import cache: replaces b8 MeshLoader::WriteToE3DM(const std::string&, const std::string&,
+ *      GeometryConfigs&) and MeshResource* MeshLoader::LoadE3DM(const std::string&, const std::string&)
+ *      -- mesh_loader.cpp:63-126 and :128-198.  Host-side file code; byte-compatible with the reference's files. ---- */
+typedef struct vkm_e3dm_config {
+    vkm_shape_out shape;        /* extent is not part of the format: zero after a read */
+    const char* name;           /* GeometryConfig::name */
+    const char* material_name;  /* GeometryConfig::material_name */
+} vkm_e3dm_config;
+int vkm_e3dm_write(const char* path, const char* mesh_name, const vkm_e3dm_config* configs, uint64_t count);
+/* Reads a file into malloc()ed configs (vertices / indices / strings); release with vkm_e3dm_free(). */
+int vkm_e3dm_read(const char* path, char* mesh_name, int mesh_name_cap, vkm_e3dm_config** out_configs,
+                  uint64_t* out_count);
+void vkm_e3dm_free(vkm_e3dm_config* configs, uint64_t count);
+
 /* Pinned host memory for callers that want full-speed PCIe transfers through the host entry points. */
 void* vkm_host_alloc(uint64_t bytes);
 void vkm_host_free(void* p);

@@ -37,6 +37,18 @@ def test_import_matches_reference_golden(name):
     assert_shapes_equal(got, golden_shapes(g))
 
 
+def test_falcon_import_then_e3dm_is_the_reference_shipped_file(tmp_path):
+    """End-to-end acceptance: tinyobj streams of falcon.obj -> CUDA import -> E3DM writer must
+    give the byte-identical file the reference ships as assets/models/falcon.e3dm."""
+    import hashlib
+
+    g = load_golden("falcon")
+    got = capi.import_shapes(g["pos"], g["nrm"], g["uv"], g["idx"], g["shape_offsets"])
+    p = str(tmp_path / "falcon.e3dm")
+    capi.e3dm_write(p, str(g["e3dm_name"]), got, [str(s) for s in g["shape_names"]], [str(s) for s in g["material_names"]])
+    assert hashlib.sha256(open(p, "rb").read()).hexdigest() == str(g["e3dm_sha256"])
+
+
 def test_cube_normals_then_tangents_golden():
     g = load_golden("cube")
     v = np.ascontiguousarray(g["vertices_in"]).view(capi.VERTEX_DTYPE).reshape(-1).copy()

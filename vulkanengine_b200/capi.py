@@ -27,6 +27,7 @@ SYMBOLS = [
     "vkm_device_count", "vkm_init", "vkm_shutdown", "vkm_last_error", "vkm_version",
     "vkm_generate_tangents", "vkm_generate_normals", "vkm_deduplicate_vertices",
     "vkm_import_shapes", "vkm_free_shape", "vkm_host_alloc", "vkm_host_free",
+    "vkm_e3dm_write", "vkm_e3dm_read", "vkm_e3dm_free",
     "vkm_plan_create", "vkm_plan_destroy", "vkm_plan_import", "vkm_plan_finish", "vkm_plan_set_timing",
     "vkm_plan_phase_name", "vkm_generate_tangents_dev", "vkm_generate_normals_dev",
     "vkm_generate_tangents_dev_noalloc",
@@ -48,6 +49,10 @@ class ShapeOut(C.Structure):
     _fields_ = [("vertex_size", C.c_uint32), ("vertex_count", C.c_uint32), ("vertices", C.c_void_p),
                 ("index_size", C.c_uint32), ("index_count", C.c_uint32), ("indices", C.c_void_p),
                 ("extent", Extent)]
+
+
+class E3dmConfig(C.Structure):
+    _fields_ = [("shape", ShapeOut), ("name", C.c_char_p), ("material_name", C.c_char_p)]
 
 
 class PlanDesc(C.Structure):
@@ -90,6 +95,11 @@ def lib():
     L.vkm_import_shapes.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p,
                                     C.c_void_p, C.c_uint32, C.POINTER(ShapeOut)]
     L.vkm_free_shape.argtypes = [C.POINTER(ShapeOut)]
+    L.vkm_e3dm_write.restype = C.c_int
+    L.vkm_e3dm_write.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(E3dmConfig), C.c_uint64]
+    L.vkm_e3dm_read.restype = C.c_int
+    L.vkm_e3dm_read.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.POINTER(E3dmConfig)), C.POINTER(C.c_uint64)]
+    L.vkm_e3dm_free.argtypes = [C.POINTER(E3dmConfig), C.c_uint64]
     L.vkm_host_alloc.restype = C.c_void_p
     L.vkm_host_alloc.argtypes = [C.c_uint64]
     L.vkm_host_free.argtypes = [C.c_void_p]
@@ -193,6 +203,45 @@ def deduplicate_vertices(vertices: np.ndarray, indices: np.ndarray):
     libc.free.argtypes = [C.c_void_p]
     libc.free(out)  # malloc()ed by the library, as the reference's Platform::AllocMemory result is
     return v, idx
+
+
+def e3dm_write(path: str, mesh_name: str, shapes: list, names: list, material_names: list) -> None:
+    """vkm_e3dm_write: the reference's WriteToE3DM file format (mesh_loader.cpp:63-126)."""
+    n = len(shapes)
+    cfgs = (E3dmConfig * max(n, 1))()
+    keep = []
+    for i, s in enumerate(shapes):
+        v = np.ascontiguousarray(s.vertices)
+        ix = np.ascontiguousarray(s.indices, np.uint32)
+        keep += [v, ix]
+        cfgs[i].shape.vertex_size, cfgs[i].shape.vertex_count, cfgs[i].shape.vertices = 64, len(v), v.ctypes.data
+        cfgs[i].shape.index_size, cfgs[i].shape.index_count, cfgs[i].shape.indices = 4, len(ix), ix.ctypes.data
+        cfgs[i].name = names[i].encode()
+        cfgs[i].material_name = material_names[i].encode()
+    _check_plain(lib().vkm_e3dm_write(path.encode(), mesh_name.encode(), cfgs, n), "vkm_e3dm_write")
+
+
+def e3dm_read(path: str):
+    """vkm_e3dm_read -> (mesh name, [ShapeResult], [config names], [material names])."""
+    L = lib()
+    cfgs = C.POINTER(E3dmConfig)()
+    cnt = C.c_uint64()
+    name = C.create_string_buffer(1024)
+    _check_plain(L.vkm_e3dm_read(path.encode(), name, 1024, C.byref(cfgs), C.byref(cnt)), "vkm_e3dm_read")
+    shapes, names, mats = [], [], []
+    for i in range(cnt.value):
+        s = cfgs[i].shape
+        shapes.append(ShapeResult(_copy_out(s.vertices, s.vertex_count * s.vertex_size, VERTEX_DTYPE),
+                                  _copy_out(s.indices, s.index_count * s.index_size, np.uint32), np.zeros(9, np.float32)))
+        names.append(cfgs[i].name.decode())
+        mats.append(cfgs[i].material_name.decode())
+    L.vkm_e3dm_free(cfgs, cnt)
+    return name.value.decode(), shapes, names, mats
+
+
+def _check_plain(rc: int, what: str) -> None:
+    if rc != VKM_OK:
+        raise VkmError(rc, what + " failed")
 
 
 class DeviceArray:
