@@ -11,6 +11,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "vkm_kernels.cuh"
@@ -536,8 +537,88 @@ struct HostCtx {
     DevBuf<uint32_t> ind, scratch, flag;
     cudaStream_t st = nullptr;
     int bound_device = -1;
+    // pinned bounce buffer + per-chunk events for the device-to-host leg of vkm_import_shapes
+    char* h_stage = nullptr;
+    uint64_t h_stage_cap = 0;
+    std::vector<cudaEvent_t> chunk_ev;
 };
 HostCtx g_ctx;
+
+// Device-to-host leg of the host entry point.  The engine wants malloc()ed buffers; a direct copy into fresh
+// pageable memory runs at a few GB/s (driver bounce buffers + first-touch page faults on one thread).  Instead
+// the results are DMA'd in 16 MiB chunks into a cached pinned buffer at PCIe speed, and a few host threads copy
+// finished chunks into the malloc()ed destinations while later chunks are still in flight.
+struct Seg {
+    uint64_t off;  // offset in the staging image
+    char* dst;
+    uint64_t bytes;
+};
+
+void copy_stage_range(const char* stage, const std::vector<Seg>& segs, uint64_t a, uint64_t b) {
+    size_t lo = 0, hi = segs.size();
+    while (lo < hi) {  // first segment that ends after a
+        const size_t mid = (lo + hi) / 2;
+        if (segs[mid].off + segs[mid].bytes <= a) lo = mid + 1; else hi = mid;
+    }
+    for (size_t i = lo; i < segs.size() && segs[i].off < b; ++i) {
+        const uint64_t s0 = std::max(a, segs[i].off), s1 = std::min(b, segs[i].off + segs[i].bytes);
+        if (s1 > s0) memcpy(segs[i].dst + (s0 - segs[i].off), stage + s0, s1 - s0);
+    }
+}
+
+int download_staged(HostCtx& c, const void* d_vertices, uint64_t vbytes, const void* d_indices, uint64_t ibytes,
+                    const std::vector<Seg>& segs) {
+    const uint64_t total = vbytes + ibytes;
+    if (total == 0) return VKM_OK;
+    constexpr uint64_t kChunk = 16ull << 20;
+    if (total > c.h_stage_cap) {
+        if (c.h_stage) cudaFreeHost(c.h_stage);
+        c.h_stage = nullptr;
+        c.h_stage_cap = 0;
+        const uint64_t want = total + total / 8;
+        if (cudaMallocHost((void**)&c.h_stage, want) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(VKM_ERR_OOM, "pinned staging buffer (%llu bytes) could not be allocated", (unsigned long long)want);
+        }
+        c.h_stage_cap = want;
+    }
+    const uint64_t nchunks = (total + kChunk - 1) / kChunk;
+    while (c.chunk_ev.size() < nchunks) {
+        cudaEvent_t e;
+        CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        c.chunk_ev.push_back(e);
+    }
+    for (uint64_t k = 0; k < nchunks; ++k) {
+        const uint64_t a = k * kChunk, b = std::min(total, a + kChunk);
+        if (a < vbytes) CU(cudaMemcpyAsync(c.h_stage + a, (const char*)d_vertices + a, std::min(b, vbytes) - a, cudaMemcpyDeviceToHost, c.st));
+        if (b > vbytes) {
+            const uint64_t ia = std::max(a, vbytes);
+            CU(cudaMemcpyAsync(c.h_stage + ia, (const char*)d_indices + (ia - vbytes), b - ia, cudaMemcpyDeviceToHost, c.st));
+        }
+        CU(cudaEventRecord(c.chunk_ev[k], c.st));
+    }
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const unsigned nthreads = (unsigned)std::min<uint64_t>(std::min(8u, hw), nchunks);
+    const int dev = c.bound_device;
+    std::vector<int> errs(nthreads, 0);
+    auto work = [&](unsigned t) {
+        cudaSetDevice(dev);
+        for (uint64_t k = t; k < nchunks; k += nthreads) {
+            if (cudaEventSynchronize(c.chunk_ev[k]) != cudaSuccess) {
+                errs[t] = 1;
+                return;
+            }
+            copy_stage_range(c.h_stage, segs, k * kChunk, std::min(total, (k + 1) * kChunk));
+        }
+    };
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < nthreads; ++t) pool.emplace_back(work, t);
+    work(0);
+    for (auto& th : pool) th.join();
+    for (int e : errs)
+        if (e) return fail(VKM_ERR_CUDA, "device-to-host copy failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return VKM_OK;
+}
 
 int ctx_bind(HostCtx& c) {
     if (vkm_device_count() == 0) return fail(VKM_ERR_NO_DEVICE, "no CUDA device: vkmesh_b200 has no CPU path");
@@ -603,6 +684,11 @@ void vkm_shutdown(void) {
     if (c.plan) { vkm_plan_destroy(c.plan); c.plan = nullptr; }
     c.pos.release(); c.nrm.release(); c.uv.release(); c.idx.release(); c.vtx.release(); c.ind.release();
     c.scratch.release(); c.flag.release();
+    if (c.h_stage) cudaFreeHost(c.h_stage);
+    c.h_stage = nullptr;
+    c.h_stage_cap = 0;
+    for (auto e : c.chunk_ev) cudaEventDestroy(e);
+    c.chunk_ev.clear();
     if (c.st) cudaStreamDestroy(c.st);
     c.st = nullptr;
     c.bound_device = -1;
@@ -720,12 +806,14 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
     if ((rc = vkm_plan_import(c.plan, c.pos.p, np, c.nrm.p, nn, c.uv.p, nt, c.idx.p, shape_off, nshapes, c.st))) return rc;
     vkm_plan_result r{};
     if ((rc = vkm_plan_finish(c.plan, &r))) return rc;
+    const uint64_t vbytes = r.total_vertices * 64, ibytes = C * 4;
+    std::vector<Seg> segs;
+    segs.reserve(2ull * nshapes);
     for (uint32_t s = 0; s < nshapes; ++s) {
         vkm_shape_out& o = out[s];
         const uint32_t v0 = r.shape_vertex_offsets[s], v1 = r.shape_vertex_offsets[s + 1];
-        const uint64_t c0 = shape_off[s], c1 = shape_off[s + 1];
         o.vertex_count = v1 - v0;
-        o.index_count = (uint32_t)(c1 - c0);
+        o.index_count = (uint32_t)(shape_off[s + 1] - shape_off[s]);
         o.extent = r.shape_extents[s];
         // malloc(): the engine frees these with free() (Platform::FrMemory, mesh_resource.cpp:13-18)
         o.vertices = malloc(std::max<uint64_t>((uint64_t)o.vertex_count * 64, 1));
@@ -734,10 +822,14 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
             for (uint32_t k = 0; k <= s; ++k) vkm_free_shape(&out[k]);
             return fail(VKM_ERR_OOM, "vkm_import_shapes: host allocation failed");
         }
-        if (o.vertex_count) CU(cudaMemcpyAsync(o.vertices, (const char*)r.d_vertices + (uint64_t)v0 * 64, (uint64_t)o.vertex_count * 64, cudaMemcpyDeviceToHost, c.st));
-        if (o.index_count) CU(cudaMemcpyAsync(o.indices, r.d_indices + c0, (uint64_t)o.index_count * 4, cudaMemcpyDeviceToHost, c.st));
+        if (o.vertex_count) segs.push_back(Seg{(uint64_t)v0 * 64, (char*)o.vertices, (uint64_t)o.vertex_count * 64});
     }
-    CU(cudaStreamSynchronize(c.st));
+    for (uint32_t s = 0; s < nshapes; ++s)
+        if (out[s].index_count) segs.push_back(Seg{vbytes + shape_off[s] * 4, (char*)out[s].indices, (uint64_t)out[s].index_count * 4});
+    if ((rc = download_staged(c, r.d_vertices, vbytes, r.d_indices, ibytes, segs))) {
+        for (uint32_t k = 0; k < nshapes; ++k) vkm_free_shape(&out[k]);
+        return rc;
+    }
     return VKM_OK;
 }
 
