@@ -57,66 +57,63 @@ def hbm_peak():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    """SM clock and throttle reasons sampled (NVML, every ~5 ms, in a thread) while the timed region runs."""
 
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, gpu_index: int):
         self.gpu = gpu_index
-        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
-        self.proc = None
+        self.samples = []  # (time, sm_mhz, reasons bitmask)
         self.t0 = self.t1 = None
+        self._stop = threading.Event()
+        self._thread = None
+        self.max_mhz = None
+        self.err = None
+
+    def _run(self):
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = self.gpu
+            if visible:
+                try:
+                    idx = int(visible.split(",")[self.gpu])
+                except (ValueError, IndexError):
+                    idx = self.gpu
+            h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+            while not self._stop.is_set():
+                self.samples.append((time.time(), float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)),
+                                     int(get_reasons(h))))
+                time.sleep(0.005)
+        except Exception as e:  # noqa: BLE001 - sampling must never break the benchmark
+            self.err = repr(e)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu=timestamp,{self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
-                                         stderr=subprocess.DEVNULL)
-        except OSError:
-            self.proc = None
+        self._thread = threading.Thread(target=self._run, daemon=True)
+        self._thread.start()
 
     def mark(self, which):
         setattr(self, which, time.time())
 
     def stop(self):
-        if self.proc:
-            self.proc.terminate()
-            try:
-                self.proc.wait(timeout=5)
-            except Exception:
-                self.proc.kill()
-        self.f.flush()
-        self.f.seek(0)
-        rows = [r.strip().split(", ") for r in self.f.read().splitlines() if r.strip()]
-        self.f.close()
-        os.unlink(self.f.name)
-        import datetime
-
-        sm, mx, reasons, inside = [], [], set(), []
-        for r in rows:
-            if len(r) < 10:
-                continue
-            try:
-                ts = datetime.datetime.strptime(r[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
-                clk, cmax = float(r[2]), float(r[3])
-            except ValueError:
-                continue
-            rec = (ts, clk, cmax, r[6:10])
-            sm.append(rec)
-            if self.t0 and self.t1 and self.t0 - 0.05 <= ts <= self.t1 + 0.05:
-                inside.append(rec)
-        use = inside if len(inside) >= 2 else sm
+        self._stop.set()
+        if self._thread:
+            self._thread.join(timeout=2)
+        inside = [x for x in self.samples if self.t0 and self.t1 and self.t0 <= x[0] <= self.t1]
+        use = inside if len(inside) >= 2 else self.samples
         if not use:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for rec in use:
-            for nme, val in zip(names, rec[3]):
-                if val.strip().lower().startswith("active"):
-                    reasons.add(nme)
-        return {"sm_mhz": float(np.median([u[1] for u in use])), "sm_max_mhz": float(max(u[2] for u in use)),
-                "reasons": sorted(reasons), "samples": len(use), "in_timed_region": len(inside) >= 2}
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0, "error": self.err}
+        mask = 0
+        for x in use:
+            mask |= x[2]
+        return {"sm_mhz": float(np.median([x[1] for x in use])), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(n for bit, n in self.REASONS.items() if mask & bit), "samples": len(use),
+                "in_timed_region": len(inside) >= 2}
 
 
 # ------------------------------------------------------------------------------------------ reference arm
@@ -179,7 +176,7 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--workload", default="highdup16m", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
