@@ -18,7 +18,8 @@ struct Status {
     uint32_t has_unmatchable;    // at least one NaN/Inf key was seen
     uint32_t capacity_exceeded;  // unique vertices > plan capacity
     uint32_t total_vertices;
-    uint32_t pad[2];
+    uint32_t has_value_dup;      // two distinct triplets carried the same value key (duplicated records, +-0 twins)
+    uint32_t pad[1];
 };
 
 // Everything a kernel of the import pipeline may touch.  Passed by value.
@@ -38,6 +39,7 @@ struct ImportArgs {
     uint32_t t1_mode;   // 0: locality-preserving home slot (key attribute index * scale), 1: scrambled hash
     uint32_t t1_sel;    // which of v / n / t is the key attribute (the largest attribute array)
     uint32_t t1_scale;  // slots per key-attribute record
+    uint4* trip;        // [m1] per slot: (v, n, t, shape) of the slot's triplet, written once by the claimer
     uint32_t* table2;  // value table: (tag << cbits | first corner); 2^cbits > ncorners, so a word is never kEmpty32
     uint32_t m2;
     uint32_t cbits;    // bits that hold the corner id in a table2 word; the remaining high bits are a hash tag
@@ -86,15 +88,13 @@ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
 
 // Home slot of a triplet.  Mode 0 keeps the order of the key attribute's indices, so that a mesh whose faces
 // are stored coherently touches the table coherently (neighbouring corners -> neighbouring slots -> shared
-// sectors); the other two indices only pick one of `scale` sub-slots.  Mode 1 is a full scramble, used when
-// mode 0 clusters (many distinct triplets per key record).
+// sectors): record k of the key attribute owns slots [k*scale, (k+1)*scale); its first variant takes the first
+// one, further variants (same record, other n/t) probe on.  Mode 1 is a full scramble, used when mode 0
+// clusters (many distinct triplets per key record).
 __device__ __forceinline__ uint32_t home_slot(const ImportArgs& a, uint32_t v, uint32_t n, uint32_t t, uint32_t sh) {
     if (a.t1_mode == 0) {
         const uint32_t key = a.t1_sel == 0 ? v : (a.t1_sel == 1 ? n : t);
-        const uint32_t o1 = a.t1_sel == 0 ? n : v;
-        const uint32_t o2 = a.t1_sel == 2 ? n : t;
-        const uint32_t sub = (mix32(o1 * 0x9E3779B1u ^ o2 * 0x85EBCA77u ^ sh) >> 8) % a.t1_scale;
-        return key * a.t1_scale + sub;  // < np|nn|nt * scale <= m1 (host guarantees no 32-bit overflow)
+        return key * a.t1_scale;  // < np|nn|nt * scale <= m1 (host guarantees no 32-bit overflow)
     }
     return reduce32((uint32_t)hash_triplet(v, n, t, sh), a.m1);
 }

@@ -5,7 +5,7 @@
 //   k_resolve_slots     A2/A3/A4  per distinct triplet (slot domain): gather 8 floats, bounding box, NaN/Inf
 //                              screening, insert the VALUE key into table2                    [T-scale]
 //   k_mark_unmatchable  A3     NaN/Inf keys: every occurrence creates a vertex (only runs if any seen)
-//   k_mark_value_firsts A3     table2 -> one flag bit per vertex-creating corner
+//   k_redo_flags_*      A3     only if value duplicates exist: rebuild the flag bits from table2
 //   k_scan_*            A3     popcount prefix over the flag bitmap (stable first-occurrence order)
 //   k_shape_bases       A8     per-shape vertex base / count
 //   k_final_index       A3     per triplet: final local vertex index
@@ -76,7 +76,11 @@ __global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
                 uint32_t cur = __ldcg(a.table1 + s);
                 if (cur == kEmpty32) {
                     const uint32_t prev = atomicCAS(a.table1 + s, kEmpty32, c);
-                    if (prev == kEmpty32) { ok = true; break; }
+                    if (prev == kEmpty32) {
+                        a.trip[s] = make_uint4(v, n, t, sh);  // read by the slot-domain passes after this kernel
+                        ok = true;
+                        break;
+                    }
                     cur = prev;
                 }
                 if (cur == c) { ok = true; break; }
@@ -133,6 +137,7 @@ __device__ __forceinline__ uint32_t insert_value(const ImportArgs& a, uint32_t c
             if (occ == c) return s;
             if (occ >= sh_begin && occ < sh_end && same_value_key(a, occ, k)) {
                 if (occ > c) atomicMin(a.table2 + s, mine);  // same tag: orders by corner
+                a.status->has_value_dup = 1;  // the later arrival of every duplicate pair lands here
                 return s;
             }
         }
@@ -160,26 +165,43 @@ __device__ __forceinline__ void box_atomics(uint32_t* e, const uint32_t mn[3], c
 __global__ void __launch_bounds__(kThreads) k_resolve_slots(ImportArgs a) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t neutral = 0x80000000u;  // enc_float(+0): the reference's box always contains the origin
-    const uint32_t padded = (a.m1 + 31) & ~31u;  // whole warps stay in the loop (warp reductions below)
-    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < padded; s += gridDim.x * blockDim.x) {
+    // One thread per PAIR of slots: in mode 0 a key record owns slots (2k, 2k+1) and the odd one is only used by
+    // a second variant of the record, so nearly every thread has exactly one triplet to resolve.
+    const uint32_t npairs = a.m1 >> 1;
+    const uint32_t padded = (npairs + 31) & ~31u;  // whole warps stay in the loop (warp reductions below)
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < padded; p += gridDim.x * blockDim.x) {
         uint32_t mn[3] = {neutral, neutral, neutral}, mx[3] = {neutral, neutral, neutral};
-        const uint32_t c = (s < a.m1) ? __ldcs(a.table1 + s) : kEmpty32;
-        const bool occupied = (c != kEmpty32);
-        uint32_t sh = 0xFFFFFFFFu;
-        if (occupied) {
-            // the slot's triplet, read back from its first corner (slot order ~ corner order: coherent gathers)
-            const int32_t* o = a.idx + 3ull * c;
-            const uint32_t tv = (uint32_t)__ldg(o), tn = (uint32_t)__ldg(o + 1), tt = (uint32_t)__ldg(o + 2);
-            sh = find_shape(a.shape_off, a.nshapes, c);
+        uint2 cc = make_uint2(kEmpty32, kEmpty32);
+        if (p < npairs) cc = __ldcs(reinterpret_cast<const uint2*>(a.table1) + p);
+        uint32_t sh = 0xFFFFFFFFu;  // shape of this thread's box contribution
+        bool mixed = false;         // the two slots belong to different shapes: use per-slot atomics
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const uint32_t c = j ? cc.y : cc.x;
+            if (c == kEmpty32) continue;
+            const uint32_t s = 2 * p + j;
+            const uint4 tr = __ldcs(a.trip + s);  // the slot's triplet, recorded by its claimer
             uint32_t k[8];
-            gather_key(a, tv, tn, tt, k);
+            gather_key(a, tr.x, tr.y, tr.z, k);
             bool bad = false;
 #pragma unroll
             for (int i = 0; i < 8; ++i) bad |= nonfinite_bits(k[i]);
+            uint32_t pmn[3] = {neutral, neutral, neutral}, pmx[3] = {neutral, neutral, neutral};
 #pragma unroll
             for (int i = 0; i < 3; ++i) {
                 // strict </> against NaN never updates the reference's box; +-Inf does
-                if ((k[i] & 0x7FFFFFFFu) <= 0x7F800000u) mn[i] = mx[i] = enc_float(__uint_as_float(k[i]));
+                if ((k[i] & 0x7FFFFFFFu) <= 0x7F800000u) pmn[i] = pmx[i] = enc_float(__uint_as_float(k[i]));
+            }
+            if (sh == 0xFFFFFFFFu || sh == tr.w) {
+                sh = tr.w;
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    mn[i] = min(mn[i], pmn[i]);
+                    mx[i] = max(mx[i], pmx[i]);
+                }
+            } else {
+                mixed = true;
+                box_atomics(a.ext_enc + 6u * tr.w, pmn, pmx);
             }
             if (bad) {
                 a.aux1[s] = kUnmatchable;
@@ -187,21 +209,26 @@ __global__ void __launch_bounds__(kThreads) k_resolve_slots(ImportArgs a) {
             } else {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) k[i] = canon_bits(k[i]);
-                a.aux1[s] = insert_value(a, c, k, sh, a.shape_off[sh], a.shape_off[sh + 1]);
+                a.aux1[s] = insert_value(a, c, k, tr.w, a.shape_off[tr.w], a.shape_off[tr.w + 1]);
+                // Speculation: no two distinct triplets share a value key (true for almost every mesh), so the
+                // first corner of every distinct triplet creates a vertex.  If a duplicate shows up anywhere,
+                // has_value_dup is raised and k_redo_flags_* rebuild the flags from the value table.
+                atomicOr(a.fbits + (c >> 5), 1u << (c & 31));
             }
         }
         // bounding box: one set of (improvement-checked) atomics per warp when its slots share a shape
-        const uint32_t any = __ballot_sync(0xFFFFFFFFu, occupied);
+        const bool have = (sh != 0xFFFFFFFFu);
+        const uint32_t any = __ballot_sync(0xFFFFFFFFu, have);
         if (any) {
             const uint32_t sh0 = __shfl_sync(0xFFFFFFFFu, sh, __ffs(any) - 1);
-            if (__all_sync(0xFFFFFFFFu, !occupied || sh == sh0)) {
+            if (__all_sync(0xFFFFFFFFu, !have || (sh == sh0 && !mixed))) {
 #pragma unroll
                 for (int i = 0; i < 3; ++i) {
                     mn[i] = __reduce_min_sync(0xFFFFFFFFu, mn[i]);
                     mx[i] = __reduce_max_sync(0xFFFFFFFFu, mx[i]);
                 }
                 if (lane == 0) box_atomics(a.ext_enc + 6u * sh0, mn, mx);
-            } else if (occupied) {
+            } else if (have) {
                 box_atomics(a.ext_enc + 6u * sh, mn, mx);
             }
         }
@@ -216,7 +243,15 @@ __global__ void __launch_bounds__(kThreads) k_mark_unmatchable(ImportArgs a) {
     }
 }
 
-__global__ void __launch_bounds__(kThreads) k_mark_value_firsts(ImportArgs a) {
+// Only when value duplicates exist: the speculative flags are wrong for the later triplet of each duplicate
+// group.  Clear them, then flag the lowest corner of every distinct value key from the value table.
+__global__ void __launch_bounds__(kThreads) k_redo_flags_clear(ImportArgs a) {
+    if (a.status->has_value_dup == 0) return;
+    for (uint32_t w = blockIdx.x * blockDim.x + threadIdx.x; w < a.nwords; w += gridDim.x * blockDim.x) a.fbits[w] = 0;
+}
+
+__global__ void __launch_bounds__(kThreads) k_redo_flags_mark(ImportArgs a) {
+    if (a.status->has_value_dup == 0) return;
     for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < a.m2; s += gridDim.x * blockDim.x) {
         const uint32_t cur = a.table2[s];
         if (cur != kEmpty32) {
@@ -325,9 +360,15 @@ __global__ void __launch_bounds__(kThreads) k_zero_lastface(ImportArgs a) {
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads) k_final_index(ImportArgs a) {
     for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < a.m1; s += gridDim.x * blockDim.x) {
-        if (a.table1[s] == kEmpty32) continue;
+        const uint32_t first = a.table1[s];
+        if (first == kEmpty32) continue;
         const uint32_t x = a.aux1[s];
         if (x == kUnmatchable) continue;
+        if (a.status->has_value_dup == 0) {  // every distinct triplet is its own vertex: coherent reads only
+            if (first >= a.ncorners) continue;
+            a.aux1[s] = rank_of(a, first) - a.vbase[find_shape(a.shape_off, a.nshapes, first)];
+            continue;
+        }
         if (x >= a.m2) continue;                      // only after an overflow; the host re-runs then
         const uint32_t word = a.table2[x];
         const uint32_t rep = (a.cbits >= 32) ? word : (word & ((1u << a.cbits) - 1u));  // first corner with this VALUE key
@@ -390,17 +431,22 @@ __device__ __forceinline__ void store_vertex(float4* dst, const uint32_t k[8]) {
 }
 
 __global__ void __launch_bounds__(kThreads) k_write_vertices(ImportArgs a) {
-    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < a.m1; s += gridDim.x * blockDim.x) {
-        const uint32_t c = __ldcs(a.table1 + s);
-        if (c == kEmpty32 || c >= a.ncorners) continue;
-        const uint32_t w = c >> 5, bits = a.fbits[w];
-        if (!((bits >> (c & 31)) & 1u)) continue;  // a value duplicate of an earlier triplet
-        const uint32_t id = a.fprefix[w] + __popc(bits & ((1u << (c & 31)) - 1u));
-        if (id >= a.vertex_capacity) continue;
-        const int32_t* o = a.idx + 3ull * c;
-        uint32_t k[8];
-        gather_key(a, (uint32_t)__ldg(o), (uint32_t)__ldg(o + 1), (uint32_t)__ldg(o + 2), k);
-        store_vertex(a.out_vtx + 4ull * id, k);
+    const uint32_t npairs = a.m1 >> 1;  // one thread per pair of slots, as in k_resolve_slots
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npairs; p += gridDim.x * blockDim.x) {
+        const uint2 cc = __ldcs(reinterpret_cast<const uint2*>(a.table1) + p);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const uint32_t c = j ? cc.y : cc.x;
+            if (c == kEmpty32 || c >= a.ncorners) continue;
+            const uint32_t w = c >> 5, bits = a.fbits[w];
+            if (!((bits >> (c & 31)) & 1u)) continue;  // a value duplicate of an earlier triplet
+            const uint32_t id = a.fprefix[w] + __popc(bits & ((1u << (c & 31)) - 1u));
+            if (id >= a.vertex_capacity) continue;
+            const uint4 tr = __ldcs(a.trip + 2 * p + j);
+            uint32_t k[8];
+            gather_key(a, tr.x, tr.y, tr.z, k);
+            store_vertex(a.out_vtx + 4ull * id, k);
+        }
     }
 }
 

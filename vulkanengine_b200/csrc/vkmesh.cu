@@ -102,6 +102,7 @@ struct vkm_plan {
     DevBuf<uint32_t> table1, table2;
     DevBuf<uint32_t> slot1, aux1, fbits, fprefix, block_sums, ext_enc, vbase, lastface, out_idx, shape_off;
     DevBuf<float4> out_vtx;
+    DevBuf<uint4> trip;
     DevBuf<Status> status;
     // pinned host mirrors
     Status* h_status = nullptr;
@@ -135,6 +136,7 @@ int plan_size_tables(vkm_plan* p, uint64_t slots) {
     if ((rc = p->table1.ensure(slots))) return rc;
     if ((rc = p->table2.ensure(slots))) return rc;
     if ((rc = p->aux1.ensure(slots))) return rc;
+    if ((rc = p->trip.ensure(slots))) return rc;
     return VKM_OK;
 }
 
@@ -169,6 +171,7 @@ int plan_enqueue(vkm_plan* p) {
     a.table1 = p->table1.p;
     a.table2 = p->table2.p;
     a.aux1 = p->aux1.p;
+    a.trip = p->trip.p;
     a.m2 = p->m2;
     a.cbits = 1;
     while (a.cbits < 32 && (1ull << a.cbits) <= (uint64_t)a.ncorners) a.cbits++;  // 2^cbits > ncorners
@@ -186,7 +189,7 @@ int plan_enqueue(vkm_plan* p) {
             a.t1_mode = 1;
             a.t1_sel = 0;
             a.t1_scale = 1;
-            a.m1 = p->m1;
+            a.m1 = p->m1 & ~1u;  // slot-domain kernels walk pairs of slots
         }
     }
     const bool T = p->timing;
@@ -205,10 +208,11 @@ int plan_enqueue(vkm_plan* p) {
     if (T) CU(cudaEventRecord(ev[PH_INSERT], st));
     k_insert_triplets<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_VALUES], st));
-    k_resolve_slots<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
+    k_resolve_slots<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_SCAN], st));
+    k_redo_flags_clear<<<grid_for(a.nwords, kThreads, dev), kThreads, 0, st>>>(a);
+    k_redo_flags_mark<<<grid_for(a.m2, kThreads, dev), kThreads, 0, st>>>(a);
     k_mark_unmatchable<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
-    k_mark_value_firsts<<<grid_for(a.m2, kThreads, dev), kThreads, 0, st>>>(a);
     const uint32_t ntiles = std::max<uint32_t>(1, (a.nwords + kScanTile - 1) / kScanTile);
     k_scan_tiles<<<ntiles, kScanThreads, 0, st>>>(a);
     k_scan_block_sums<<<1, kScanThreads, 0, st>>>(a, ntiles);
@@ -219,7 +223,7 @@ int plan_enqueue(vkm_plan* p) {
     k_final_index<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
     k_write_indices<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_VERTICES], st));
-    k_write_vertices<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
+    k_write_vertices<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
     k_write_unmatchable_vertices<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_TANGENTS], st));
     k_per_vertex_frames<0><<<grid_for(a.vertex_capacity, kThreads, dev), kThreads, 0, st>>>(
@@ -311,7 +315,7 @@ void vkm_plan_destroy(vkm_plan* p) {
     if (p->pending && p->done) cudaEventSynchronize(p->done);
     p->table1.release(); p->table2.release(); p->slot1.release(); p->aux1.release(); p->fbits.release();
     p->fprefix.release(); p->block_sums.release(); p->ext_enc.release(); p->vbase.release(); p->lastface.release();
-    p->out_idx.release(); p->shape_off.release(); p->out_vtx.release(); p->status.release();
+    p->out_idx.release(); p->shape_off.release(); p->out_vtx.release(); p->trip.release(); p->status.release();
     if (p->h_status) cudaFreeHost(p->h_status);
     if (p->h_vbase) cudaFreeHost(p->h_vbase);
     if (p->h_ext) cudaFreeHost(p->h_ext);
