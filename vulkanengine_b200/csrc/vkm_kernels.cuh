@@ -417,56 +417,8 @@ __global__ void __launch_bounds__(kThreads) k_write_indices(ImportArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Vertex records (A2/A8).  Slot domain: the slot whose first corner carries a flag bit writes the 64-byte
-// Vertex3D at the corner's rank.  Slot order ~ corner order for coherent meshes, so the 64-byte records of
-// neighbouring threads land next to each other.  NaN/Inf corners (every occurrence is a vertex) are
-// written by the corner-domain k_write_unmatchable_vertices, which only runs when any exist.
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void store_vertex(float4* dst, const uint32_t k[8]) {
-    // Vertex3D: position @0, normal @12, texcoord @24, color @32 (zero), tangent @48 (filled by the tangent pass)
-    __stcs(dst + 0, make_float4(__uint_as_float(k[0]), __uint_as_float(k[1]), __uint_as_float(k[2]), __uint_as_float(k[3])));
-    __stcs(dst + 1, make_float4(__uint_as_float(k[4]), __uint_as_float(k[5]), __uint_as_float(k[6]), __uint_as_float(k[7])));
-    __stcs(dst + 2, make_float4(0.f, 0.f, 0.f, 0.f));
-    __stcs(dst + 3, make_float4(0.f, 0.f, 0.f, 0.f));
-}
-
-__global__ void __launch_bounds__(kThreads) k_write_vertices(ImportArgs a) {
-    const uint32_t npairs = a.m1 >> 1;  // one thread per pair of slots, as in k_resolve_slots
-    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npairs; p += gridDim.x * blockDim.x) {
-        const uint2 cc = __ldcs(reinterpret_cast<const uint2*>(a.table1) + p);
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const uint32_t c = j ? cc.y : cc.x;
-            if (c == kEmpty32 || c >= a.ncorners) continue;
-            const uint32_t w = c >> 5, bits = a.fbits[w];
-            if (!((bits >> (c & 31)) & 1u)) continue;  // a value duplicate of an earlier triplet
-            const uint32_t id = a.fprefix[w] + __popc(bits & ((1u << (c & 31)) - 1u));
-            if (id >= a.vertex_capacity) continue;
-            const uint4 tr = __ldcs(a.trip + 2 * p + j);
-            uint32_t k[8];
-            gather_key(a, tr.x, tr.y, tr.z, k);
-            store_vertex(a.out_vtx + 4ull * id, k);
-        }
-    }
-}
-
-__global__ void __launch_bounds__(kThreads) k_write_unmatchable_vertices(ImportArgs a) {
-    if (a.status->has_unmatchable == 0) return;
-    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < a.ncorners; c += gridDim.x * blockDim.x) {
-        if (a.aux1[a.slot1[c]] != kUnmatchable) continue;
-        const uint32_t id = rank_of(a, c);
-        if (id >= a.vertex_capacity) continue;
-        const int32_t* o = a.idx + 3ull * c;
-        uint32_t k[8];
-        gather_key(a, (uint32_t)__ldg(o), (uint32_t)__ldg(o + 1), (uint32_t)__ldg(o + 2), k);
-        store_vertex(a.out_vtx + 4ull * id, k);
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
-// Tangents / normals: one thread per vertex evaluates the winning triangle.
-// Arithmetic mirrors geometry.cpp:26-47 / :72-75 operation by operation with round-to-nearest
-// intrinsics, which the compiler never contracts into FMAs (the reference CPU build has none).
+// Tangent / normal arithmetic.  Mirrors geometry.cpp:26-47 / :72-75 operation by operation with
+// round-to-nearest intrinsics, which the compiler never contracts into FMAs (the reference CPU build has none).
 // ---------------------------------------------------------------------------------------------
 struct Tri {
     float px[3], py[3], pz[3], u[3], v[3];
@@ -513,6 +465,82 @@ __device__ __forceinline__ float3 normal_of(const Tri& t) {
     return normalize_rn(nx, ny, nz);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Vertex records (A2/A8).  Slot domain: the slot whose first corner carries a flag bit writes the 64-byte
+// Vertex3D at the corner's rank.  Slot order ~ corner order for coherent meshes, so the 64-byte records of
+// neighbouring threads land next to each other.  NaN/Inf corners (every occurrence is a vertex) are
+// written by the corner-domain k_write_unmatchable_vertices, which only runs when any exist.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void store_vertex(float4* dst, const uint32_t k[8], float4 tangent) {
+    // Vertex3D: position @0, normal @12, texcoord @24, color @32 (zero), tangent @48
+    __stcs(dst + 0, make_float4(__uint_as_float(k[0]), __uint_as_float(k[1]), __uint_as_float(k[2]), __uint_as_float(k[3])));
+    __stcs(dst + 1, make_float4(__uint_as_float(k[4]), __uint_as_float(k[5]), __uint_as_float(k[6]), __uint_as_float(k[7])));
+    __stcs(dst + 2, make_float4(0.f, 0.f, 0.f, 0.f));
+    __stcs(dst + 3, tangent);
+}
+
+// Tangents can be produced while the vertex record is written when every vertex was created by exactly the
+// triplet its corners carry: no value duplicates (a later triplet with equal values could differ from the stored
+// first-seen bits in the sign of a zero) and no NaN/Inf keys (their corners point at vertex 0).  Then the
+// winning triangle's corners read pos[v] / uv[t] of their own triplets, which ARE the stored vertices' bits.
+__device__ __forceinline__ bool tangents_fusable(const ImportArgs& a) {
+    return a.status->has_value_dup == 0 && a.status->has_unmatchable == 0;
+}
+
+__global__ void __launch_bounds__(kThreads) k_write_vertices(ImportArgs a) {
+    const uint32_t npairs = a.m1 >> 1;  // one thread per pair of slots, as in k_resolve_slots
+    const bool fuse = tangents_fusable(a);
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npairs; p += gridDim.x * blockDim.x) {
+        const uint2 cc = __ldcs(reinterpret_cast<const uint2*>(a.table1) + p);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const uint32_t c = j ? cc.y : cc.x;
+            if (c == kEmpty32 || c >= a.ncorners) continue;
+            const uint32_t w = c >> 5, bits = a.fbits[w];
+            if (!((bits >> (c & 31)) & 1u)) continue;  // a value duplicate of an earlier triplet
+            const uint32_t id = a.fprefix[w] + __popc(bits & ((1u << (c & 31)) - 1u));
+            if (id >= a.vertex_capacity) continue;
+            const uint4 tr = __ldcs(a.trip + 2 * p + j);
+            uint32_t k[8];
+            gather_key(a, tr.x, tr.y, tr.z, k);
+            float4 tangent = make_float4(0.f, 0.f, 0.f, 0.f);  // a vertex no triangle references keeps zeros
+            const uint32_t lf = fuse ? a.lastface[id] : 0;
+            if (lf) {
+                // the winning (highest-numbered) triangle: its corners' slots give their triplets
+                const uint32_t* sl = a.slot1 + 3ull * (lf - 1);
+                Tri t;
+#pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                    const uint4 ct = a.trip[sl[q]];
+                    const float* pp = a.pos + 3ull * min(ct.x, a.np - 1);
+                    const float2 uu = __ldg(reinterpret_cast<const float2*>(a.uv) + min(ct.z, a.nt - 1));
+                    t.px[q] = __ldg(pp); t.py[q] = __ldg(pp + 1); t.pz[q] = __ldg(pp + 2);
+                    t.u[q] = uu.x; t.v[q] = uu.y;
+                }
+                tangent = tangent_of(t);
+            }
+            store_vertex(a.out_vtx + 4ull * id, k, tangent);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) k_write_unmatchable_vertices(ImportArgs a) {
+    if (a.status->has_unmatchable == 0) return;
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < a.ncorners; c += gridDim.x * blockDim.x) {
+        if (a.aux1[a.slot1[c]] != kUnmatchable) continue;
+        const uint32_t id = rank_of(a, c);
+        if (id >= a.vertex_capacity) continue;
+        const int32_t* o = a.idx + 3ull * c;
+        uint32_t k[8];
+        gather_key(a, (uint32_t)__ldg(o), (uint32_t)__ldg(o + 1), (uint32_t)__ldg(o + 2), k);
+        store_vertex(a.out_vtx + 4ull * id, k, make_float4(0.f, 0.f, 0.f, 0.f));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Tangents / normals as a separate pass: one thread per vertex evaluates the winning triangle from the
+// finished vertex records (the stand-alone utilities, and imports with value duplicates or NaN/Inf keys).
+// ---------------------------------------------------------------------------------------------
 // lastface[v] = 1 + highest triangle id that references vertex v (0 = unreferenced).
 __global__ void __launch_bounds__(kThreads) k_last_face(const uint32_t* __restrict__ indices, uint32_t index_count,
                                                         uint32_t vertex_count, uint32_t* lastface,
@@ -536,7 +564,9 @@ __global__ void __launch_bounds__(kThreads) k_per_vertex_frames(float4* vtx, con
                                                                 const uint32_t* __restrict__ total_ptr, uint32_t total_max,
                                                                 const uint32_t* __restrict__ shape_off,
                                                                 const uint32_t* __restrict__ vbase, uint32_t nshapes,
-                                                                uint32_t vertex_limit) {
+                                                                uint32_t vertex_limit, const Status* fused_status) {
+    // import pipeline: nothing to do when k_write_vertices already produced the tangents
+    if (fused_status && fused_status->has_value_dup == 0 && fused_status->has_unmatchable == 0) return;
     const uint32_t total = total_ptr ? min(*total_ptr, total_max) : total_max;
     for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < total; v += gridDim.x * blockDim.x) {
         const uint32_t lf = lastface[v];

@@ -228,7 +228,7 @@ int plan_enqueue(vkm_plan* p) {
     if (T) CU(cudaEventRecord(ev[PH_TANGENTS], st));
     k_per_vertex_frames<0><<<grid_for(a.vertex_capacity, kThreads, dev), kThreads, 0, st>>>(
         a.out_vtx, a.out_idx, a.lastface, &p->status.p->total_vertices, a.vertex_capacity, a.shape_off, a.vbase,
-        a.nshapes, a.vertex_capacity);
+        a.nshapes, a.vertex_capacity, p->status.p);
     CU(cudaEventRecord(ev[PH_COUNT], st));
     p->slot_busy[slot] = true;
     p->seq++;
@@ -447,10 +447,10 @@ static int frames_dev(int mode, uint32_t vertex_count, void* d_vertices, uint32_
                                                                              d_scratch, d_bad);
     if (mode == 0)
         k_per_vertex_frames<0><<<grid_for(vertex_count, kThreads, dev), kThreads, 0, st>>>(
-            (float4*)d_vertices, d_indices, d_scratch, nullptr, vertex_count, nullptr, nullptr, 1, vertex_count);
+            (float4*)d_vertices, d_indices, d_scratch, nullptr, vertex_count, nullptr, nullptr, 1, vertex_count, nullptr);
     else
         k_per_vertex_frames<1><<<grid_for(vertex_count, kThreads, dev), kThreads, 0, st>>>(
-            (float4*)d_vertices, d_indices, d_scratch, nullptr, vertex_count, nullptr, nullptr, 1, vertex_count);
+            (float4*)d_vertices, d_indices, d_scratch, nullptr, vertex_count, nullptr, nullptr, 1, vertex_count, nullptr);
     CU(cudaGetLastError());
     return VKM_OK;
 }
@@ -520,7 +520,7 @@ int vkm_generate_tangents_dev_noalloc(uint32_t vertex_count, void* d_vertices, u
     k_last_face<<<grid_for(index_count / 3, kThreads, dev), kThreads, 0, st>>>(d_indices, index_count, vertex_count,
                                                                              scratch, flag);
     k_per_vertex_frames<0><<<grid_for(vertex_count, kThreads, dev), kThreads, 0, st>>>(
-        (float4*)d_vertices, d_indices, scratch, nullptr, vertex_count, nullptr, nullptr, 1, vertex_count);
+        (float4*)d_vertices, d_indices, scratch, nullptr, vertex_count, nullptr, nullptr, 1, vertex_count, nullptr);
     CU(cudaGetLastError());
     return VKM_OK;
 }
