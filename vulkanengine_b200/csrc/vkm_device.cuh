@@ -143,6 +143,17 @@ __device__ __forceinline__ uint32_t rank_of(const ImportArgs& a, uint32_t c) {
     return a.fprefix[w] + __popc(a.fbits[w] & ((1u << (c & 31)) - 1u));
 }
 
+// A "clean" import has no value duplicates (two distinct triplets with the same canonical 8 floats) and no NaN/Inf
+// keys.  Then every distinct triplet IS one vertex, created by the very triplet its corners carry, and:
+//   - a corner's final index is the rank of its slot's first corner (no second-level lookup);
+//   - tangents can be produced while the vertex record is written: the winning triangle's corners read
+//     pos[v] / uv[t] of their own triplets, which are bit-identical to the stored vertices (a value duplicate
+//     could differ from the stored first-seen bits in the sign of a zero; a NaN/Inf corner points at vertex 0).
+// The flags are final once k_resolve_slots has finished.
+__device__ __forceinline__ bool import_is_clean(const ImportArgs& a) {
+    return a.status->has_value_dup == 0 && a.status->has_unmatchable == 0;
+}
+
 // Loads the 8 live floats of a corner's expanded vertex (position, normal, texcoord) as raw bits.
 // Indices are clamped so that a flagged bad index can never fault.
 __device__ __forceinline__ void gather_key(const ImportArgs& a, uint32_t v, uint32_t n, uint32_t t, uint32_t k[8]) {

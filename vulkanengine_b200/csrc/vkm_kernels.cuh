@@ -359,6 +359,7 @@ __global__ void __launch_bounds__(kThreads) k_zero_lastface(ImportArgs a) {
 // Final indices
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads) k_final_index(ImportArgs a) {
+    if (import_is_clean(a)) return;  // clean import: k_write_indices ranks the slot's first corner itself
     for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < a.m1; s += gridDim.x * blockDim.x) {
         const uint32_t first = a.table1[s];
         if (first == kEmpty32) continue;
@@ -379,6 +380,7 @@ __global__ void __launch_bounds__(kThreads) k_final_index(ImportArgs a) {
 }
 
 __global__ void __launch_bounds__(kThreads) k_write_indices(ImportArgs a) {
+    const bool clean = import_is_clean(a);
     const uint32_t ngroups = (a.ncorners + 3) >> 2;
     for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
         const uint32_t c0 = g << 2;
@@ -391,8 +393,14 @@ __global__ void __launch_bounds__(kThreads) k_write_indices(ImportArgs a) {
             for (int i = 0; i < 4 && c0 + i < a.ncorners; ++i) s[i] = a.slot1[c0 + i];
         }
         uint32_t li[4];
+        if (clean) {
+            // every distinct triplet is its own vertex: global rank of the slot's first corner (coherent gathers)
 #pragma unroll
-        for (int i = 0; i < 4; ++i) li[i] = (c0 + i < a.ncorners) ? a.aux1[s[i]] : 0;
+            for (int i = 0; i < 4; ++i) li[i] = (c0 + i < a.ncorners) ? rank_of(a, min(a.table1[s[i]], a.ncorners - 1)) : 0;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) li[i] = (c0 + i < a.ncorners) ? a.aux1[s[i]] : 0;
+        }
         uint32_t sh = find_shape(a.shape_off, a.nshapes, c0);
         uint32_t sh_end = a.shape_off[sh + 1], base = a.vbase[sh];
 #pragma unroll
@@ -404,7 +412,8 @@ __global__ void __launch_bounds__(kThreads) k_write_indices(ImportArgs a) {
                 sh_end = a.shape_off[sh + 1];
                 base = a.vbase[sh];
             }
-            if (li[i] == kUnmatchable) li[i] = 0;  // mesh_loader.cpp:285 default-inserts value 0 for a NaN key
+            if (clean) li[i] -= base;                   // global rank -> index local to the shape
+            else if (li[i] == kUnmatchable) li[i] = 0;  // mesh_loader.cpp:285 default-inserts value 0 for a NaN key
             const uint32_t gv = base + li[i];
             if (gv < a.vertex_capacity) atomicMax(a.lastface + gv, c / 3 + 1);
         }
@@ -479,17 +488,9 @@ __device__ __forceinline__ void store_vertex(float4* dst, const uint32_t k[8], f
     __stcs(dst + 3, tangent);
 }
 
-// Tangents can be produced while the vertex record is written when every vertex was created by exactly the
-// triplet its corners carry: no value duplicates (a later triplet with equal values could differ from the stored
-// first-seen bits in the sign of a zero) and no NaN/Inf keys (their corners point at vertex 0).  Then the
-// winning triangle's corners read pos[v] / uv[t] of their own triplets, which ARE the stored vertices' bits.
-__device__ __forceinline__ bool tangents_fusable(const ImportArgs& a) {
-    return a.status->has_value_dup == 0 && a.status->has_unmatchable == 0;
-}
-
 __global__ void __launch_bounds__(kThreads) k_write_vertices(ImportArgs a) {
     const uint32_t npairs = a.m1 >> 1;  // one thread per pair of slots, as in k_resolve_slots
-    const bool fuse = tangents_fusable(a);
+    const bool fuse = import_is_clean(a);
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npairs; p += gridDim.x * blockDim.x) {
         const uint2 cc = __ldcs(reinterpret_cast<const uint2*>(a.table1) + p);
 #pragma unroll
