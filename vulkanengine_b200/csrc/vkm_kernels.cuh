@@ -37,6 +37,9 @@ __device__ __forceinline__ bool same_triplet(const int32_t* __restrict__ idx, ui
     return (uint32_t)__ldg(o) == v && (uint32_t)__ldg(o + 1) == n && (uint32_t)__ldg(o + 2) == t;
 }
 
+// ADDR: 0/1/2 = mode 0 keyed on v / n / t, 3 = mode 1 (scrambled).  MULTI: more than one shape in the stream.
+// Specialising removes the per-corner mode/shape branching; the kernel is instruction-issue bound.
+template <int ADDR, bool MULTI>
 __global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
     const uint32_t ngroups = (a.ncorners + 3) >> 2;
     for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
@@ -52,25 +55,33 @@ __global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
 #pragma unroll
             for (int i = 0; i < 12; ++i) w[i] = (c0 + i / 3 < a.ncorners) ? __ldg(a.idx + 3ull * c0 + i) : 0;
         }
-        uint32_t sh = find_shape(a.shape_off, a.nshapes, min(c0, a.ncorners - 1));
-        uint32_t sh_begin = a.shape_off[sh], sh_end = a.shape_off[sh + 1];
+        uint32_t sh = 0, sh_begin = 0, sh_end = a.ncorners;
+        if (MULTI) {
+            sh = find_shape(a.shape_off, a.nshapes, min(c0, a.ncorners - 1));
+            sh_begin = a.shape_off[sh];
+            sh_end = a.shape_off[sh + 1];
+        }
         uint32_t slots[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const uint32_t c = c0 + i;
             slots[i] = 0;
             if (c >= a.ncorners) continue;
-            if (c >= sh_end) {
+            if (MULTI && c >= sh_end) {
                 sh = find_shape(a.shape_off, a.nshapes, c);
                 sh_begin = a.shape_off[sh];
                 sh_end = a.shape_off[sh + 1];
             }
             const uint32_t v = (uint32_t)w[3 * i], n = (uint32_t)w[3 * i + 1], t = (uint32_t)w[3 * i + 2];
-            if (v >= a.np || n >= a.nn || t >= a.nt) {
+            if (v >= a.np || n >= a.nn || t >= a.nt) {  // negative ints are huge as unsigned
                 a.status->bad_index = 1;
                 continue;
             }
-            uint32_t s = home_slot(a, v, n, t, sh);
+            uint32_t s;
+            if (ADDR == 0) s = v * 2;
+            else if (ADDR == 1) s = n * 2;
+            else if (ADDR == 2) s = t * 2;
+            else s = reduce32((uint32_t)hash_triplet(v, n, t, sh), a.m1);
             bool ok = false;
             for (int probe = 0; probe < kMaxProbe; ++probe) {
                 uint32_t cur = __ldcg(a.table1 + s);

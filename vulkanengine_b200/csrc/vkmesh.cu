@@ -206,7 +206,23 @@ int plan_enqueue(vkm_plan* p) {
         CU(cudaMemset2DAsync(reinterpret_cast<char*>(a.ext_enc) + 3, 4, 0x80, 1, (size_t)a.nshapes * 6, st));
     }
     if (T) CU(cudaEventRecord(ev[PH_INSERT], st));
-    k_insert_triplets<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
+    {
+        const unsigned g1 = grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev);
+        const int addr = a.t1_mode == 0 ? (int)a.t1_sel : 3;
+        const bool multi = a.nshapes > 1;
+#define VKM_K1(A, M) k_insert_triplets<A, M><<<g1, kThreads, 0, st>>>(a)
+        switch (addr * 2 + (multi ? 1 : 0)) {
+            case 0: VKM_K1(0, false); break;
+            case 1: VKM_K1(0, true); break;
+            case 2: VKM_K1(1, false); break;
+            case 3: VKM_K1(1, true); break;
+            case 4: VKM_K1(2, false); break;
+            case 5: VKM_K1(2, true); break;
+            case 6: VKM_K1(3, false); break;
+            default: VKM_K1(3, true); break;
+        }
+#undef VKM_K1
+    }
     if (T) CU(cudaEventRecord(ev[PH_VALUES], st));
     k_resolve_slots<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_SCAN], st));
