@@ -173,7 +173,7 @@ __device__ __forceinline__ void box_atomics(uint32_t* e, const uint32_t mn[3], c
 // over distinct triplets equals the box over all corners), screen NaN/Inf, insert the value key.
 // Slot order follows the key attribute's index order, so the gathers are as coherent as the mesh.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads) k_resolve_slots(ImportArgs a) {
+__global__ void __launch_bounds__(kThreads, 8) k_resolve_slots(ImportArgs a) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t neutral = 0x80000000u;  // enc_float(+0): the reference's box always contains the origin
     // One thread per PAIR of slots: in mode 0 a key record owns slots (2k, 2k+1) and the odd one is only used by
@@ -499,7 +499,7 @@ __device__ __forceinline__ void store_vertex(float4* dst, const uint32_t k[8], f
     __stcs(dst + 3, tangent);
 }
 
-__global__ void __launch_bounds__(kThreads) k_write_vertices(ImportArgs a) {
+__global__ void __launch_bounds__(kThreads, 8) k_write_vertices(ImportArgs a) {
     const uint32_t npairs = a.m1 >> 1;  // one thread per pair of slots, as in k_resolve_slots
     const bool fuse = import_is_clean(a);
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npairs; p += gridDim.x * blockDim.x) {
