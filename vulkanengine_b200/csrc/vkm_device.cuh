@@ -19,7 +19,7 @@ struct Status {
     uint32_t capacity_exceeded;  // unique vertices > plan capacity
     uint32_t total_vertices;
     uint32_t has_value_dup;      // two distinct triplets carried the same value key (duplicated records, +-0 twins)
-    uint32_t pad[1];
+    uint32_t has_displaced;      // mode 0: some triplet sits outside its key record's own slot pair
 };
 
 // Everything a kernel of the import pipeline may touch.  Passed by value.
@@ -39,7 +39,8 @@ struct ImportArgs {
     uint32_t t1_mode;   // 0: locality-preserving home slot (key attribute index * scale), 1: scrambled hash
     uint32_t t1_sel;    // which of v / n / t is the key attribute (the largest attribute array)
     uint32_t t1_scale;  // slots per key-attribute record
-    uint4* trip;        // [m1] per slot: (v, n, t, shape) of the slot's triplet, written once by the claimer
+    uint4* trip;        // [m1 / 2] mode 0: (v, n, t, shape) of the FIRST variant of key record p, written by the thread
+                        // that claims slot 2p as its home slot; dense (every referenced record has one), never cleared
     uint32_t* table2;  // value table: (tag << cbits | first corner); 2^cbits > ncorners, so a word is never kEmpty32
     uint32_t m2;
     uint32_t cbits;    // bits that hold the corner id in a table2 word; the remaining high bits are a hash tag
@@ -152,6 +153,20 @@ __device__ __forceinline__ uint32_t rank_of(const ImportArgs& a, uint32_t c) {
 // The flags are final once k_resolve_slots has finished.
 __device__ __forceinline__ bool import_is_clean(const ImportArgs& a) {
     return a.status->has_value_dup == 0 && a.status->has_unmatchable == 0;
+}
+
+// The triplet stored in slot s (whose first corner is c).  In mode 0, while no triplet was displaced out of its own
+// slot pair, an even slot 2p can only hold the first variant of key record p, and that variant's claimer wrote
+// trip[p]: one aligned 16-byte read.  Every other case (second variants in odd slots, displaced entries, mode 1)
+// reads the triplet back from the slot's first corner in the index stream -- always exact, just a gather.
+__device__ __forceinline__ uint4 slot_triplet(const ImportArgs& a, uint32_t s, uint32_t c, bool fast) {
+    if (fast && !(s & 1u)) return a.trip[s >> 1];
+    const int32_t* o = a.idx + 3ull * min(c, a.ncorners - 1);
+    return make_uint4((uint32_t)__ldg(o), (uint32_t)__ldg(o + 1), (uint32_t)__ldg(o + 2),
+                      find_shape(a.shape_off, a.nshapes, c));
+}
+__device__ __forceinline__ bool trip_is_fast(const ImportArgs& a) {
+    return a.t1_mode == 0 && a.status->has_displaced == 0;
 }
 
 // Loads the 8 live floats of a corner's expanded vertex (position, normal, texcoord) as raw bits.

@@ -88,7 +88,11 @@ __global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
                 if (cur == kEmpty32) {
                     const uint32_t prev = atomicCAS(a.table1 + s, kEmpty32, c);
                     if (prev == kEmpty32) {
-                        a.trip[s] = make_uint4(v, n, t, sh);  // read by the slot-domain passes after this kernel
+                        if (ADDR != 3) {
+                            // first variant of its key record: leave the triplet for the slot-domain passes
+                            if (probe == 0) a.trip[s >> 1] = make_uint4(v, n, t, sh);
+                            else if (probe >= 2) a.status->has_displaced = 1;  // landed outside its own slot pair
+                        }
                         ok = true;
                         break;
                     }
@@ -180,6 +184,7 @@ __global__ void __launch_bounds__(kThreads, 8) k_resolve_slots(ImportArgs a) {
     // a second variant of the record, so nearly every thread has exactly one triplet to resolve.
     const uint32_t npairs = a.m1 >> 1;
     const uint32_t padded = (npairs + 31) & ~31u;  // whole warps stay in the loop (warp reductions below)
+    const bool fast = trip_is_fast(a);
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < padded; p += gridDim.x * blockDim.x) {
         uint32_t mn[3] = {neutral, neutral, neutral}, mx[3] = {neutral, neutral, neutral};
         uint2 cc = make_uint2(kEmpty32, kEmpty32);
@@ -191,7 +196,7 @@ __global__ void __launch_bounds__(kThreads, 8) k_resolve_slots(ImportArgs a) {
             const uint32_t c = j ? cc.y : cc.x;
             if (c == kEmpty32) continue;
             const uint32_t s = 2 * p + j;
-            const uint4 tr = __ldcs(a.trip + s);  // the slot's triplet, recorded by its claimer
+            const uint4 tr = slot_triplet(a, s, c, fast);
             uint32_t k[8];
             gather_key(a, tr.x, tr.y, tr.z, k);
             bool bad = false;
@@ -502,6 +507,7 @@ __device__ __forceinline__ void store_vertex(float4* dst, const uint32_t k[8], f
 __global__ void __launch_bounds__(kThreads, 8) k_write_vertices(ImportArgs a) {
     const uint32_t npairs = a.m1 >> 1;  // one thread per pair of slots, as in k_resolve_slots
     const bool fuse = import_is_clean(a);
+    const bool fast = trip_is_fast(a);
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npairs; p += gridDim.x * blockDim.x) {
         const uint2 cc = __ldcs(reinterpret_cast<const uint2*>(a.table1) + p);
 #pragma unroll
@@ -512,7 +518,7 @@ __global__ void __launch_bounds__(kThreads, 8) k_write_vertices(ImportArgs a) {
             if (!((bits >> (c & 31)) & 1u)) continue;  // a value duplicate of an earlier triplet
             const uint32_t id = a.fprefix[w] + __popc(bits & ((1u << (c & 31)) - 1u));
             if (id >= a.vertex_capacity) continue;
-            const uint4 tr = __ldcs(a.trip + 2 * p + j);
+            const uint4 tr = slot_triplet(a, 2 * p + j, c, fast);
             uint32_t k[8];
             gather_key(a, tr.x, tr.y, tr.z, k);
             float4 tangent = make_float4(0.f, 0.f, 0.f, 0.f);  // a vertex no triangle references keeps zeros
@@ -523,7 +529,8 @@ __global__ void __launch_bounds__(kThreads, 8) k_write_vertices(ImportArgs a) {
                 Tri t;
 #pragma unroll
                 for (int q = 0; q < 3; ++q) {
-                    const uint4 ct = a.trip[sl[q]];
+                    // the corner's own triplet, via its slot's record when that is a single aligned read
+                    const uint4 ct = slot_triplet(a, sl[q], 3 * (lf - 1) + q, fast);
                     const float* pp = a.pos + 3ull * min(ct.x, a.np - 1);
                     const float2 uu = __ldg(reinterpret_cast<const float2*>(a.uv) + min(ct.z, a.nt - 1));
                     t.px[q] = __ldg(pp); t.py[q] = __ldg(pp + 1); t.pz[q] = __ldg(pp + 2);

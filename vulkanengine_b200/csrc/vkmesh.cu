@@ -136,7 +136,7 @@ int plan_size_tables(vkm_plan* p, uint64_t slots) {
     if ((rc = p->table1.ensure(slots))) return rc;
     if ((rc = p->table2.ensure(slots))) return rc;
     if ((rc = p->aux1.ensure(slots))) return rc;
-    if ((rc = p->trip.ensure(slots))) return rc;
+    if ((rc = p->trip.ensure(slots / 2 + 1))) return rc;
     return VKM_OK;
 }
 
