@@ -151,6 +151,34 @@ void vkm_plan_set_timing(vkm_plan* plan, int enabled);
 /* Names of the phases reported in vkm_plan_result.phase_ms (NULL past the last). */
 const char* vkm_plan_phase_name(int phase);
 
+/* ---- renderer handoff as a headless device buffer.  Replaces the bookkeeping of
+ *      GeometrySystem::AcquireGeometryFromConfig -> VulkanRendererBackend::CreateGeometry -> UploadDataRange
+ *      (geometry_system.cpp:136-176; vulkan.cpp:15-27, 691-725): one global vertex buffer and one global index
+ *      buffer, first-fit byte ranges (Freelist::AllocateBlock, core/utils/freelist.cpp:144-159), and the
+ *      (offset, size) pair per geometry that the draw call binds with (vulkan.cpp:664-672).  The buffers are plain
+ *      device memory; the Vulkan external-memory import is unavailable on this box. ---- */
+typedef struct vkm_rangealloc vkm_rangealloc;       /* first-fit range allocator (host bookkeeping only) */
+vkm_rangealloc* vkm_rangealloc_create(uint64_t total_bytes);
+void vkm_rangealloc_destroy(vkm_rangealloc* a);
+uint64_t vkm_rangealloc_alloc(vkm_rangealloc* a, uint64_t size);  /* lowest fitting offset, UINT64_MAX if none */
+int vkm_rangealloc_free(vkm_rangealloc* a, uint64_t offset, uint64_t size);
+uint64_t vkm_rangealloc_free_space(const vkm_rangealloc* a);
+
+typedef struct vkm_geometry_pool vkm_geometry_pool;
+typedef struct vkm_pool_geometry {
+    uint64_t vertex_offset, vertex_bytes; /* byte range in the global vertex buffer */
+    uint64_t index_offset, index_bytes;   /* byte range in the global index buffer (u32 indices) */
+    uint32_t vertex_count, index_count;
+} vkm_pool_geometry;
+int vkm_pool_create(int device, uint64_t vertex_bytes, uint64_t index_bytes, vkm_geometry_pool** out);
+void vkm_pool_destroy(vkm_geometry_pool* pool);
+const void* vkm_pool_vertex_buffer(const vkm_geometry_pool* pool);
+const void* vkm_pool_index_buffer(const vkm_geometry_pool* pool);
+/* Places shape `shape` of a finished import (vkm_plan_finish) into the pool: device-to-device copies on `stream`. */
+int vkm_pool_acquire(vkm_geometry_pool* pool, const vkm_plan_result* result, const uint64_t* shape_corner_offsets,
+                     uint32_t shape, vkm_pool_geometry* out, void* stream);
+int vkm_pool_release(vkm_geometry_pool* pool, const vkm_pool_geometry* geometry);
+
 /* Device-resident Geometry::GenerateTangents / GenerateNormals (geometry.cpp:20-82) on caller-owned device
  * buffers; `d_scratch` must hold vertex_count u32 (it is overwritten). */
 int vkm_generate_tangents_dev(uint32_t vertex_count, void* d_vertices, uint32_t index_count,

@@ -266,6 +266,41 @@ def test_sharded_batch_driver_matches_oracle():
     assert got == want
 
 
+def test_headless_renderer_handoff_pool():
+    """f2: finished shapes land in first-fit ranges of one global vertex / index device buffer, byte-identical."""
+    import ctypes as C
+
+    L = capi.lib()
+    m = synth.concat([synth.grid(20), synth.uv_sphere(8, 16), synth.grid(5)])
+    d = [capi.DeviceArray(0, a) for a in (m.pos, m.nrm, m.uv, m.idx)]
+    plan = capi.Plan(0, m.corners, max_attrib=max(len(m.pos), len(m.nrm), len(m.uv)), max_shapes=3)
+    plan.import_async(d[0].ptr, len(m.pos), d[1].ptr, len(m.nrm), d[2].ptr, len(m.uv), d[3].ptr, m.shape_offsets)
+    r = plan.finish()
+    want = oracle_of(m)
+    pool = C.c_void_p()
+    capi._check_plain(L.vkm_pool_create(0, 1 << 20, 1 << 18, C.byref(pool)), "vkm_pool_create")
+    so = np.ascontiguousarray(m.shape_offsets, np.uint64)
+    geos = []
+    for s in (2, 0, 1):  # any order: ranges are handed out first fit
+        g = capi.PoolGeometry()
+        capi._check_plain(L.vkm_pool_acquire(pool, C.byref(r), so.ctypes.data, s, C.byref(g), None), "vkm_pool_acquire")
+        geos.append((s, g))
+    capi._check(L.vkm_dev_sync(0))
+    voff = 0
+    for s, g in geos:
+        assert g.vertex_offset == voff and g.vertex_bytes == 64 * len(want[s].vertices)
+        voff += g.vertex_bytes
+        v = capi.download(0, L.vkm_pool_vertex_buffer(pool) + g.vertex_offset, capi.VERTEX_DTYPE, g.vertex_count)
+        i = capi.download(0, L.vkm_pool_index_buffer(pool) + g.index_offset, np.uint32, g.index_count)
+        ok, msg = vertices_equal(v, want[s].vertices)
+        assert ok, msg
+        assert np.array_equal(i, want[s].indices)
+    big = capi.PoolGeometry()
+    assert L.vkm_pool_release(pool, C.byref(geos[0][1])) == 0
+    L.vkm_pool_destroy(pool)
+    plan.destroy()
+
+
 # ---------------------------------------------------------------- full-size property checks (no oracle run)
 def test_config3_16m_properties():
     """16.7M-triangle high-duplication grid: too slow for the CPU oracle inside the test budget, so check

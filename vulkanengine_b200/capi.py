@@ -31,6 +31,9 @@ SYMBOLS = [
     "vkm_plan_create", "vkm_plan_destroy", "vkm_plan_import", "vkm_plan_finish", "vkm_plan_set_timing",
     "vkm_plan_phase_name", "vkm_generate_tangents_dev", "vkm_generate_normals_dev",
     "vkm_generate_tangents_dev_noalloc",
+    "vkm_rangealloc_create", "vkm_rangealloc_destroy", "vkm_rangealloc_alloc", "vkm_rangealloc_free",
+    "vkm_rangealloc_free_space", "vkm_pool_create", "vkm_pool_destroy", "vkm_pool_vertex_buffer",
+    "vkm_pool_index_buffer", "vkm_pool_acquire", "vkm_pool_release",
     "vkm_dev_alloc", "vkm_dev_free", "vkm_dev_upload", "vkm_dev_download", "vkm_dev_sync",
 ]
 
@@ -53,6 +56,11 @@ class ShapeOut(C.Structure):
 
 class E3dmConfig(C.Structure):
     _fields_ = [("shape", ShapeOut), ("name", C.c_char_p), ("material_name", C.c_char_p)]
+
+
+class PoolGeometry(C.Structure):
+    _fields_ = [("vertex_offset", C.c_uint64), ("vertex_bytes", C.c_uint64), ("index_offset", C.c_uint64),
+                ("index_bytes", C.c_uint64), ("vertex_count", C.c_uint32), ("index_count", C.c_uint32)]
 
 
 class PlanDesc(C.Structure):
@@ -119,6 +127,26 @@ def lib():
         fn.argtypes = [C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
     L.vkm_generate_tangents_dev_noalloc.restype = C.c_int
     L.vkm_generate_tangents_dev_noalloc.argtypes = [C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]
+    L.vkm_rangealloc_create.restype = C.c_void_p
+    L.vkm_rangealloc_create.argtypes = [C.c_uint64]
+    L.vkm_rangealloc_destroy.argtypes = [C.c_void_p]
+    L.vkm_rangealloc_alloc.restype = C.c_uint64
+    L.vkm_rangealloc_alloc.argtypes = [C.c_void_p, C.c_uint64]
+    L.vkm_rangealloc_free.restype = C.c_int
+    L.vkm_rangealloc_free.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64]
+    L.vkm_rangealloc_free_space.restype = C.c_uint64
+    L.vkm_rangealloc_free_space.argtypes = [C.c_void_p]
+    L.vkm_pool_create.restype = C.c_int
+    L.vkm_pool_create.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_void_p)]
+    L.vkm_pool_destroy.argtypes = [C.c_void_p]
+    L.vkm_pool_vertex_buffer.restype = C.c_void_p
+    L.vkm_pool_vertex_buffer.argtypes = [C.c_void_p]
+    L.vkm_pool_index_buffer.restype = C.c_void_p
+    L.vkm_pool_index_buffer.argtypes = [C.c_void_p]
+    L.vkm_pool_acquire.restype = C.c_int
+    L.vkm_pool_acquire.argtypes = [C.c_void_p, C.POINTER(PlanResult), C.c_void_p, C.c_uint32, C.POINTER(PoolGeometry), C.c_void_p]
+    L.vkm_pool_release.restype = C.c_int
+    L.vkm_pool_release.argtypes = [C.c_void_p, C.POINTER(PoolGeometry)]
     L.vkm_dev_alloc.restype = C.c_int
     L.vkm_dev_alloc.argtypes = [C.c_int, C.c_uint64, C.POINTER(C.c_void_p)]
     L.vkm_dev_free.argtypes = [C.c_int, C.c_void_p]
