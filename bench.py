@@ -32,7 +32,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "mesh triangles/sec (dedup+normals+tangents)"
 UNIT = "triangles/s"
-KERNELS_PER_STEP = 15  # our kernels per import (memset nodes not counted); see vkmesh.cu plan_enqueue
+KERNELS_PER_STEP = 7  # our kernels per clean import (clear, insert, resolve, scan x2, indices, vertices); vkmesh.cu plan_enqueue
 FALLBACK_HBM_GBS = 6650.0
 
 WORKLOADS = {

@@ -6,8 +6,8 @@
 //                              screening, insert the VALUE key into table2                    [T-scale]
 //   k_mark_unmatchable  A3     NaN/Inf keys: every occurrence creates a vertex (only runs if any seen)
 //   k_redo_flags_*      A3     only if value duplicates exist: rebuild the flag bits from table2
-//   k_scan_*            A3     popcount prefix over the flag bitmap (stable first-occurrence order)
-//   k_shape_bases       A8     per-shape vertex base / count
+//   k_scan_tiles/finish A3/A8  popcount prefix over the flag bitmap (stable first-occurrence order), per-shape
+//                              vertex bases, lastface reset
 //   k_final_index       A3     per triplet: final local vertex index
 //   k_write_indices     A3/A5  per corner: index buffer + atomicMax(last face per vertex)   [C-scale]
 //   k_write_vertices    A2/A8  stable compaction: 64-byte Vertex3D records
@@ -21,6 +21,25 @@
 namespace vkm {
 
 constexpr int kThreads = 256;
+
+// ---------------------------------------------------------------------------------------------
+// Per-import reset of the scratch in ONE launch (six memset nodes cost more launch gaps than bytes on small
+// meshes): tables -> empty, flag bitmap -> 0, boxes -> enc(+0) (GeometryExtent extent{}, mesh_loader.cpp:230),
+// status -> 0.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_clear(ImportArgs a) {
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    const uint4 ff = make_uint4(kEmpty32, kEmpty32, kEmpty32, kEmpty32);
+    uint4* t1 = reinterpret_cast<uint4*>(a.table1);
+    for (uint32_t i = tid; i < (a.m1 >> 2); i += nth) t1[i] = ff;
+    for (uint32_t i = (a.m1 & ~3u) + tid; i < a.m1; i += nth) a.table1[i] = kEmpty32;
+    uint4* t2 = reinterpret_cast<uint4*>(a.table2);
+    for (uint32_t i = tid; i < (a.m2 >> 2); i += nth) t2[i] = ff;
+    for (uint32_t i = (a.m2 & ~3u) + tid; i < a.m2; i += nth) a.table2[i] = kEmpty32;
+    for (uint32_t i = tid; i <= a.nwords; i += nth) a.fbits[i] = 0;
+    for (uint32_t i = tid; i < a.nshapes * 6u; i += nth) a.ext_enc[i] = 0x80000000u;
+    if (tid < sizeof(Status) / 4) reinterpret_cast<uint32_t*>(a.status)[tid] = 0;
+}
 
 // ---------------------------------------------------------------------------------------------
 // K1: triplet insert.  Each thread owns 4 consecutive corners = 48 bytes = three 128-bit loads.
@@ -322,29 +341,40 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_tiles(ImportArgs a) {
     if (threadIdx.x == 0) a.block_sums[blockIdx.x] = total;
 }
 
-__global__ void __launch_bounds__(kScanThreads) k_scan_block_sums(ImportArgs a, uint32_t nblocks) {
-    __shared__ uint32_t carry;
-    if (threadIdx.x == 0) carry = 0;
+// Second (last) scan launch, one block per tile.  Every block re-derives its own offset and the grand total
+// from the few thousand tile sums (cheaper than a third launch), writes its tile's exclusive prefixes, zeroes
+// its share of lastface[0, total), and the first blocks also rank the shape boundaries straight from the
+// bitmap (so no block has to wait for another block's prefixes).
+__global__ void __launch_bounds__(kScanThreads) k_scan_finish(ImportArgs a, uint32_t ntiles) {
+    __shared__ uint32_t red[2][32];
+    uint32_t before = 0, all = 0;
+    for (uint32_t i = threadIdx.x; i < ntiles; i += kScanThreads) {
+        const uint32_t x = a.block_sums[i];
+        all += x;
+        if (i < blockIdx.x) before += x;
+    }
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+        before += __shfl_xor_sync(0xFFFFFFFFu, before, d);
+        all += __shfl_xor_sync(0xFFFFFFFFu, all, d);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        red[0][threadIdx.x >> 5] = before;
+        red[1][threadIdx.x >> 5] = all;
+    }
     __syncthreads();
-    for (uint32_t b0 = 0; b0 < nblocks; b0 += kScanThreads) {
-        const uint32_t i = b0 + threadIdx.x;
-        const uint32_t x = (i < nblocks) ? a.block_sums[i] : 0;
-        uint32_t total;
-        const uint32_t ex = block_exclusive_scan(x, &total);
-        const uint32_t c = carry;
-        if (i < nblocks) a.block_sums[i] = c + ex;
-        __syncthreads();
-        if (threadIdx.x == 0) carry = c + total;
-        __syncthreads();
+    before = all = 0;
+#pragma unroll
+    for (int w = 0; w < kScanThreads / 32; ++w) {
+        before += red[0][w];
+        all += red[1][w];
     }
-    if (threadIdx.x == 0) {
-        a.fprefix[a.nwords] = carry;  // rank(ncorners) when ncorners % 32 == 0
-        a.status->total_vertices = carry;
-        if (carry > a.vertex_capacity) a.status->capacity_exceeded = 1;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        a.fprefix[a.nwords] = all;  // rank(ncorners) when ncorners % 32 == 0
+        a.status->total_vertices = all;
+        if (all > a.vertex_capacity) a.status->capacity_exceeded = 1;
     }
-}
-
-__global__ void __launch_bounds__(kScanThreads) k_scan_write(ImportArgs a) {
+    // this tile's prefixes
     const uint32_t base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
     uint32_t pc[kScanItems];
     uint32_t sum = 0;
@@ -353,22 +383,28 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_write(ImportArgs a) {
         pc[i] = (base + i < a.nwords) ? __popc(a.fbits[base + i]) : 0;
         sum += pc[i];
     }
-    uint32_t run = a.block_sums[blockIdx.x] + block_exclusive_scan(sum, nullptr);
+    uint32_t run = before + block_exclusive_scan(sum, nullptr);
 #pragma unroll
     for (int i = 0; i < kScanItems; ++i) {
         if (base + i < a.nwords) a.fprefix[base + i] = run;
         run += pc[i];
     }
-}
-
-__global__ void k_shape_bases(ImportArgs a) {
-    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s <= a.nshapes; s += gridDim.x * blockDim.x)
-        a.vbase[s] = rank_of(a, a.shape_off[s]);
-}
-
-__global__ void __launch_bounds__(kThreads) k_zero_lastface(ImportArgs a) {
-    const uint32_t n = min(a.status->total_vertices, a.vertex_capacity);
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) a.lastface[i] = 0;
+    // lastface[0, total) = 0
+    const uint32_t nv = min(all, a.vertex_capacity);
+    for (uint32_t i = blockIdx.x * kScanThreads + threadIdx.x; i < nv; i += ntiles * kScanThreads) a.lastface[i] = 0;
+    // shape boundaries: one warp per shape, ranks computed from tile sums + the bitmap itself
+    const uint32_t gwarp = (blockIdx.x * kScanThreads + threadIdx.x) >> 5, nwarps = (ntiles * kScanThreads) >> 5;
+    const uint32_t lane = threadIdx.x & 31;
+    for (uint32_t sidx = gwarp; sidx <= a.nshapes; sidx += nwarps) {
+        const uint32_t c = a.shape_off[sidx];
+        const uint32_t w = c >> 5, tile = w / kScanTile;
+        uint32_t r = 0;
+        for (uint32_t i = lane; i < tile; i += 32) r += a.block_sums[i];
+        for (uint32_t i = tile * kScanTile + lane; i < w; i += 32) r += __popc(a.fbits[i]);
+#pragma unroll
+        for (int d = 16; d; d >>= 1) r += __shfl_xor_sync(0xFFFFFFFFu, r, d);
+        if (lane == 0) a.vbase[sidx] = r + __popc(a.fbits[w] & ((1u << (c & 31)) - 1u));
+    }
 }
 
 // ---------------------------------------------------------------------------------------------

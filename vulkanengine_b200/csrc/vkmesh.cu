@@ -99,6 +99,9 @@ struct vkm_plan {
     cudaStream_t last_stream = nullptr;
     uint32_t m1 = 0, m2 = 0;       // allocated slots
     uint32_t t1_mode = 0;          // sticky: 0 = locality-preserving triplet table, 1 = scrambled (after clustering)
+    bool assume_clean = false;     // the previous finished import had no value duplicates / NaN-Inf keys
+    bool force_full = false;       // re-run in progress: launch the complete schedule
+    bool ran_full = false;         // what the import in flight was launched with
     DevBuf<uint32_t> table1, table2;
     DevBuf<uint32_t> slot1, aux1, fbits, fprefix, block_sums, ext_enc, vbase, lastface, out_idx, shape_off;
     DevBuf<float4> out_vtx;
@@ -193,18 +196,12 @@ int plan_enqueue(vkm_plan* p) {
         }
     }
     const bool T = p->timing;
+    // Dirty-only kernels (value duplicates, NaN/Inf keys) are not even launched while the plan's previous import
+    // was clean; vkm_plan_finish() checks the status block and re-runs with the full schedule if that was wrong.
+    const bool full = p->force_full || !p->assume_clean;
+    p->ran_full = full;
     if (T) CU(cudaEventRecord(ev[PH_CLEAR], st));
-    CU(cudaMemsetAsync(p->status.p, 0, sizeof(Status), st));
-    CU(cudaMemsetAsync(a.table1, 0xFF, (uint64_t)a.m1 * 4, st));
-    CU(cudaMemsetAsync(a.table2, 0xFF, (uint64_t)a.m2 * 4, st));
-    CU(cudaMemsetAsync(a.fbits, 0, ((uint64_t)a.nwords + 1) * 4, st));
-    // encoded +0.0 everywhere: GeometryExtent extent{} (mesh_loader.cpp:230)
-    CU(cudaMemsetAsync(a.ext_enc, 0, (uint64_t)a.nshapes * 6 * 4, st));
-    {
-        // 0x80000000 pattern = enc_float(+0); memset can only write bytes, so set the top byte of each word
-        // with a strided 2D memset.
-        CU(cudaMemset2DAsync(reinterpret_cast<char*>(a.ext_enc) + 3, 4, 0x80, 1, (size_t)a.nshapes * 6, st));
-    }
+    k_clear<<<grid_for(std::max(a.m1, a.m2) / 4, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_INSERT], st));
     {
         const unsigned g1 = grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev);
@@ -226,25 +223,25 @@ int plan_enqueue(vkm_plan* p) {
     if (T) CU(cudaEventRecord(ev[PH_VALUES], st));
     k_resolve_slots<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_SCAN], st));
-    k_redo_flags_clear<<<grid_for(a.nwords, kThreads, dev), kThreads, 0, st>>>(a);
-    k_redo_flags_mark<<<grid_for(a.m2, kThreads, dev), kThreads, 0, st>>>(a);
-    k_mark_unmatchable<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
+    if (full) {
+        k_redo_flags_clear<<<grid_for(a.nwords, kThreads, dev), kThreads, 0, st>>>(a);
+        k_redo_flags_mark<<<grid_for(a.m2, kThreads, dev), kThreads, 0, st>>>(a);
+        k_mark_unmatchable<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
+    }
     const uint32_t ntiles = std::max<uint32_t>(1, (a.nwords + kScanTile - 1) / kScanTile);
     k_scan_tiles<<<ntiles, kScanThreads, 0, st>>>(a);
-    k_scan_block_sums<<<1, kScanThreads, 0, st>>>(a, ntiles);
-    k_scan_write<<<ntiles, kScanThreads, 0, st>>>(a);
-    k_shape_bases<<<grid_for((uint64_t)a.nshapes + 1, 128, dev), 128, 0, st>>>(a);
-    k_zero_lastface<<<grid_for(a.vertex_capacity, kThreads, dev), kThreads, 0, st>>>(a);
+    k_scan_finish<<<ntiles, kScanThreads, 0, st>>>(a, ntiles);
     if (T) CU(cudaEventRecord(ev[PH_INDICES], st));
-    k_final_index<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
+    if (full) k_final_index<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
     k_write_indices<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_VERTICES], st));
     k_write_vertices<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
-    k_write_unmatchable_vertices<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
+    if (full) k_write_unmatchable_vertices<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_TANGENTS], st));
-    k_per_vertex_frames<0><<<grid_for(a.vertex_capacity, kThreads, dev), kThreads, 0, st>>>(
-        a.out_vtx, a.out_idx, a.lastface, &p->status.p->total_vertices, a.vertex_capacity, a.shape_off, a.vbase,
-        a.nshapes, a.vertex_capacity, p->status.p);
+    if (full)
+        k_per_vertex_frames<0><<<grid_for(a.vertex_capacity, kThreads, dev), kThreads, 0, st>>>(
+            a.out_vtx, a.out_idx, a.lastface, &p->status.p->total_vertices, a.vertex_capacity, a.shape_off, a.vbase,
+            a.nshapes, a.vertex_capacity, p->status.p);
     CU(cudaEventRecord(ev[PH_COUNT], st));
     p->slot_busy[slot] = true;
     p->seq++;
@@ -414,6 +411,15 @@ int vkm_plan_finish(vkm_plan* p, vkm_plan_result* r) {
             if ((rc = plan_enqueue(p))) return rc;
             continue;
         }
+        const bool dirty = s.has_value_dup || s.has_unmatchable;
+        if (dirty && !p->ran_full) {  // the short schedule was launched for a mesh that needs the general path
+            p->force_full = true;
+            const int rc = plan_enqueue(p);
+            p->force_full = false;
+            if (rc) return rc;
+            continue;
+        }
+        p->assume_clean = !dirty;
         if (s.capacity_exceeded) return fail(VKM_ERR_CAPACITY, "import: %u unique vertices exceed the plan capacity %llu", s.total_vertices, (unsigned long long)p->desc.max_vertices);
         break;
     }
