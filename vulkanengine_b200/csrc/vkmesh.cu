@@ -4,7 +4,11 @@
 
 #include <cuda_runtime.h>
 
+#include <sys/mman.h>
+#include <unistd.h>
+
 #include <algorithm>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -45,6 +49,33 @@ int fail(int code, const char* fmt, ...) {
     } while (0)
 
 constexpr uint64_t kMaxCorners = 4000000000ull;
+
+// VKM_TRACE=1 prints a host-side time line of the host entry points to stderr.
+struct Trace {
+    bool on;
+    std::chrono::steady_clock::time_point t0;
+    Trace() : on(getenv("VKM_TRACE") != nullptr), t0(std::chrono::steady_clock::now()) {}
+    void mark(const char* what) {
+        if (!on) return;
+        const auto t = std::chrono::steady_clock::now();
+        fprintf(stderr, "[vkm] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t - t0).count());
+        t0 = t;
+    }
+};
+
+// Large result buffers are malloc()ed (the engine free()s them) but first-touch page faults on 4 KiB pages cost
+// more than the PCIe transfer; asking for transparent huge pages on the interior of the block removes most of them.
+void* malloc_result(uint64_t bytes) {
+    void* p = malloc(std::max<uint64_t>(bytes, 1));
+#ifdef MADV_HUGEPAGE
+    if (p && bytes >= (8ull << 20)) {
+        const uintptr_t a = ((uintptr_t)p + (2u << 20) - 1) & ~(uintptr_t)((2u << 20) - 1);
+        const uintptr_t e = ((uintptr_t)p + bytes) & ~(uintptr_t)((2u << 20) - 1);
+        if (e > a) madvise((void*)a, e - a, MADV_HUGEPAGE);
+    }
+#endif
+    return p;
+}
 
 int sm_count(int device) {
     static int cached[64] = {0};
@@ -806,6 +837,7 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
     if (C > 0 && (!pos || !nrm || !uv || !idx)) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: null input stream");
     std::lock_guard<std::mutex> lk(g_ctx.mu);
     HostCtx& c = g_ctx;
+    Trace tr;
     int rc = ctx_bind(c);
     if (rc) return rc;
     const uint64_t max_attrib = std::max(np, std::max(nn, nt));
@@ -828,10 +860,12 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
     if (nn) CU(cudaMemcpyAsync(c.nrm.p, nrm, nn * 12, cudaMemcpyHostToDevice, c.st));
     if (nt) CU(cudaMemcpyAsync(c.uv.p, uv, nt * 8, cudaMemcpyHostToDevice, c.st));
     if (C) CU(cudaMemcpyAsync(c.idx.p, idx, C * 12, cudaMemcpyHostToDevice, c.st));
+    tr.mark("enqueue H2D");
     c.plan->t1_mode = 0;  // every host call is a new mesh: try the coherent addressing first
     if ((rc = vkm_plan_import(c.plan, c.pos.p, np, c.nrm.p, nn, c.uv.p, nt, c.idx.p, shape_off, nshapes, c.st))) return rc;
     vkm_plan_result r{};
     if ((rc = vkm_plan_finish(c.plan, &r))) return rc;
+    tr.mark("H2D + kernels (finish)");
     const uint64_t vbytes = r.total_vertices * 64, ibytes = C * 4;
     std::vector<Seg> segs;
     segs.reserve(2ull * nshapes);
@@ -842,8 +876,8 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
         o.index_count = (uint32_t)(shape_off[s + 1] - shape_off[s]);
         o.extent = r.shape_extents[s];
         // malloc(): the engine frees these with free() (Platform::FrMemory, mesh_resource.cpp:13-18)
-        o.vertices = malloc(std::max<uint64_t>((uint64_t)o.vertex_count * 64, 1));
-        o.indices = malloc(std::max<uint64_t>((uint64_t)o.index_count * 4, 1));
+        o.vertices = malloc_result((uint64_t)o.vertex_count * 64);
+        o.indices = malloc_result((uint64_t)o.index_count * 4);
         if (!o.vertices || !o.indices) {
             for (uint32_t k = 0; k <= s; ++k) vkm_free_shape(&out[k]);
             return fail(VKM_ERR_OOM, "vkm_import_shapes: host allocation failed");
@@ -852,10 +886,12 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
     }
     for (uint32_t s = 0; s < nshapes; ++s)
         if (out[s].index_count) segs.push_back(Seg{vbytes + shape_off[s] * 4, (char*)out[s].indices, (uint64_t)out[s].index_count * 4});
+    tr.mark("malloc results");
     if ((rc = download_staged(c, r.d_vertices, vbytes, r.d_indices, ibytes, segs))) {
         for (uint32_t k = 0; k < nshapes; ++k) vkm_free_shape(&out[k]);
         return rc;
     }
+    tr.mark("D2H + copy-out");
     return VKM_OK;
 }
 
