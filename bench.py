@@ -87,8 +87,15 @@ class ClockSampler:
             get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
                 pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
             while not self._stop.is_set():
-                self.samples.append((time.time(), float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)),
-                                     int(get_reasons(h))))
+                try:
+                    clk = float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                    try:
+                        why = int(get_reasons(h))
+                    except Exception as e:  # noqa: BLE001 - reasons are optional, the clock is not
+                        why, self.err = 0, repr(e)
+                    self.samples.append((time.time(), clk, why))
+                except Exception as e:  # noqa: BLE001 - one failed query must not end the sampling
+                    self.err = repr(e)
                 time.sleep(0.005)
         except Exception as e:  # noqa: BLE001 - sampling must never break the benchmark
             self.err = repr(e)
@@ -113,7 +120,7 @@ class ClockSampler:
             mask |= x[2]
         return {"sm_mhz": float(np.median([x[1] for x in use])), "sm_max_mhz": self.max_mhz,
                 "reasons": sorted(n for bit, n in self.REASONS.items() if mask & bit), "samples": len(use),
-                "in_timed_region": len(inside) >= 2}
+                "in_timed_region": len(inside) >= 2, "error": self.err}
 
 
 # ------------------------------------------------------------------------------------------ reference arm

@@ -196,7 +196,7 @@ __device__ __forceinline__ void box_atomics(uint32_t* e, const uint32_t mn[3], c
 // over distinct triplets equals the box over all corners), screen NaN/Inf, insert the value key.
 // Slot order follows the key attribute's index order, so the gathers are as coherent as the mesh.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 8) k_resolve_slots(ImportArgs a) {
+__global__ void __launch_bounds__(kThreads, 8) k_resolve_slots(ImportArgs a, bool write_aux) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t neutral = 0x80000000u;  // enc_float(+0): the reference's box always contains the origin
     // One thread per PAIR of slots: in mode 0 a key record owns slots (2k, 2k+1) and the odd one is only used by
@@ -238,13 +238,15 @@ __global__ void __launch_bounds__(kThreads, 8) k_resolve_slots(ImportArgs a) {
                 mixed = true;
                 box_atomics(a.ext_enc + 6u * tr.w, pmn, pmx);
             }
+            // aux1 (value-table slot per triplet) only feeds the dirty-only kernels: the short schedule skips it
             if (bad) {
-                a.aux1[s] = kUnmatchable;
+                if (write_aux) a.aux1[s] = kUnmatchable;
                 a.status->has_unmatchable = 1;
             } else {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) k[i] = canon_bits(k[i]);
-                a.aux1[s] = insert_value(a, c, k, tr.w, a.shape_off[tr.w], a.shape_off[tr.w + 1]);
+                const uint32_t s2 = insert_value(a, c, k, tr.w, a.shape_off[tr.w], a.shape_off[tr.w + 1]);
+                if (write_aux) a.aux1[s] = s2;
                 // Speculation: no two distinct triplets share a value key (true for almost every mesh), so the
                 // first corner of every distinct triplet creates a vertex.  If a duplicate shows up anywhere,
                 // has_value_dup is raised and k_redo_flags_* rebuild the flags from the value table.

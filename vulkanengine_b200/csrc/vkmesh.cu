@@ -252,7 +252,7 @@ int plan_enqueue(vkm_plan* p) {
 #undef VKM_K1
     }
     if (T) CU(cudaEventRecord(ev[PH_VALUES], st));
-    k_resolve_slots<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
+    k_resolve_slots<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a, full);
     if (T) CU(cudaEventRecord(ev[PH_SCAN], st));
     if (full) {
         k_redo_flags_clear<<<grid_for(a.nwords, kThreads, dev), kThreads, 0, st>>>(a);
