@@ -24,6 +24,7 @@ extern "C" {
 #define VKM_ERR_CUDA 4        /* a CUDA call failed; see vkm_last_error() */
 #define VKM_ERR_NO_DEVICE 5   /* no CUDA device: there is no CPU path */
 #define VKM_ERR_CAPACITY 6    /* a plan's fixed capacity was exceeded */
+#define VKM_ERR_UNSUPPORTED 7 /* OBJ construct that is left to the caller's CPU parser */
 
 /* Engine::Vertex3D -- engine/src/renderer/renderer_types.hpp:13-19 (64 bytes, packed floats). */
 typedef struct vkm_vertex3d {
@@ -93,6 +94,26 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
                       const int32_t* idx_vnt, const uint64_t* shape_corner_offsets, uint32_t nshapes,
                       vkm_shape_out* out);
 void vkm_free_shape(vkm_shape_out* shape);
+
+/* ---- OBJ text -> tinyobj-shaped streams on the GPU.  Replaces, for `v`/`vn`/`vt` records, triangle and quad
+ *      faces, `o`/`g` shapes and `usemtl`, the call tinyobj::LoadObj(&attributes, &shapes, &materials, ...) in
+ *      MeshLoader::LoadOBJ (mesh_loader.cpp:219; parser tinyobj.hpp:2557-3115) -- same floats (the parser's own
+ *      decimal routine is reproduced), same index_t streams, same shape split and names.  Polygons with more than
+ *      four corners and l / p / vw / t records return VKM_ERR_UNSUPPORTED: the caller keeps its CPU parser for
+ *      those files.  .mtl files are not read: `usemtl_names[i]` is the name in force at shape i's first face (the
+ *      engine uses material_ids[0], mesh_loader.cpp:231) for the caller to look up. ---- */
+typedef struct vkm_obj_streams {
+    float* pos;   uint64_t np;  /* attrib_t::vertices  (malloc) */
+    float* nrm;   uint64_t nn;  /* attrib_t::normals */
+    float* uv;    uint64_t nt;  /* attrib_t::texcoords */
+    int32_t* idx_vnt;           /* concatenated index_t streams, 3 ints per corner (v, n, t), -1 = absent */
+    uint64_t* shape_corner_offsets; /* nshapes + 1 */
+    uint32_t nshapes;
+    char** shape_names;         /* shape_t::name */
+    char** usemtl_names;
+} vkm_obj_streams;
+int vkm_parse_obj(int device, const char* text, uint64_t len, vkm_obj_streams* out);
+void vkm_free_obj_streams(vkm_obj_streams* streams);
 
 /* ---- E3DM import cache: replaces b8 MeshLoader::WriteToE3DM(const std::string&, const std::string&,
  *      GeometryConfigs&) and MeshResource* MeshLoader::LoadE3DM(const std::string&, const std::string&)

@@ -1,0 +1,145 @@
+"""GPU tests of the OBJ text parser: vkm_parse_obj against the reference's own tinyobj
+(oracle/_ref/libvkref.so, ref_parse_obj) on the same text -- floats bit for bit, index streams, shape split,
+names.  The expected values come from running the reference parser on the GPU box itself."""
+import numpy as np
+import pytest
+
+from oracle import refcpu
+from vulkanengine_b200 import capi, synth
+
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not refcpu.available(), reason="oracle/_ref/libvkref.so not built")]
+
+
+def compare(text: str, tmp_path, name="m"):
+    p = tmp_path / (name + ".obj")
+    p.write_bytes(text.encode())
+    want = refcpu.parse_obj(str(p))
+    got = capi.parse_obj(text.encode())
+    for a, b, what in [(got.pos, want.pos, "v"), (got.nrm, want.nrm, "vn"), (got.uv, want.uv, "vt")]:
+        assert a.shape == b.shape, what
+        ua, ub = a.view(np.uint32), b.view(np.uint32)
+        same = (ua == ub) | (np.isnan(a) & np.isnan(b))
+        assert same.all(), f"{what}: first difference at {np.argwhere(~same)[0]}: {a[~same][0]!r} vs {b[~same][0]!r}"
+    assert np.array_equal(got.idx, want.idx)
+    assert np.array_equal(got.shape_offsets, want.shape_offsets)
+    assert got.shape_names == want.shape_names
+    return got, want
+
+
+def test_synthetic_meshes_round_trip(tmp_path):
+    for i, m in enumerate([synth.uv_sphere(12, 20), synth.concat([synth.grid(9), synth.grid(4)]), synth.adversarial(12)]):
+        got, want = compare(synth.to_obj_text(m), tmp_path, f"s{i}")
+        assert np.array_equal(got.idx, m.idx)
+
+
+NUMBERS = ["1", "-1.", ".5", "+.25e1", "1e-3", "1E+2", "123456789.123456789", "0.1234567890123456789", "1e400", "1e-400",
+           "-0", "-0.0", "abc", "1.5x", "3.14159265358979", "2.718281828e0", "-7.25E-2", "1e", "1e+", "000.125",
+           "4.9406564584124654e-324", "1.7976931348623157e308", "0.30000000000000004", "16777217", "1e22", "1e23",
+           "9007199254740993", "0.000001", "0.0000001", "0.00000001", "123.456e-7", "+5", "-.75", "5.", "1.0000001"]
+
+
+def test_number_formats_match_tinyobj_bit_for_bit(tmp_path):
+    rng = np.random.default_rng(3)
+    lines = []
+    for i in range(0, len(NUMBERS) - 2, 1):
+        lines.append(f"v {NUMBERS[i]} {NUMBERS[i + 1]} {NUMBERS[i + 2]}")
+    for _ in range(400):  # random decimal strings with 1..25 significant digits and odd exponents
+        parts = []
+        for _ in range(3):
+            nd = int(rng.integers(1, 26))
+            digs = "".join(str(int(d)) for d in rng.integers(0, 10, nd))
+            dot = int(rng.integers(0, nd + 1))
+            s = digs[:dot] + "." + digs[dot:] if rng.random() < 0.8 else digs
+            if rng.random() < 0.3:
+                s += ("e" if rng.random() < 0.5 else "E") + str(int(rng.integers(-45, 45)))
+            parts.append(("-" if rng.random() < 0.3 else "") + s)
+        lines.append("vn " + " ".join(parts))
+        lines.append("vt " + " ".join(parts[:2]))
+    lines.append("v 1 2")            # missing z -> 0
+    lines.append("v 1 2 3 0.5 0.25 1")  # vertex colours are ignored here
+    lines.append("vt 0.5 0.5 0.0")     # w ignored
+    lines += ["f 1 2 3"]
+    compare("\n".join(lines) + "\n", tmp_path)
+
+
+TRICKY = """# comment line
+mtllib tricky.mtl
+\tv 0 0 0
+v 1 0 0\r
+v 1 1 0
+v 0 1 0
+v 0.5 0.5 1
+v 2 0 0
+v 2 3 0
+vt 0 0
+vt 1 0
+vt 1 1
+vt 0 1
+vn 0 0 1
+vn 0 1 0
+
+f 1 2 3
+f 1/1 2/2 3/3
+f 1//1 2//1 3//2
+f 1/1/1 2/2/1 3/3/2
+o first object  with spaces
+usemtl matA
+f -5 -4 -3
+f -5/-4/-2 -4/-3/-2 -3/-2/-1
+f 1 2 3 4
+f 2 6 7 3
+f 1/1/1 2/2/1 3/3/1 4/4/1
+g grp1   grp2\tgrp3
+f 1 2 5
+usemtl matB
+f 2 3 5
+g
+g empty_then_named
+o
+usemtl matA
+o second
+f 3 4 5
+s off
+f 4 1 5
+"""
+
+
+def test_tricky_text_matches_tinyobj(tmp_path):
+    (tmp_path / "tricky.mtl").write_text("newmtl matA\nKd 1 0 0\nnewmtl matB\nKd 0 1 0\n")
+    got, want = compare(TRICKY, tmp_path, "tricky")
+    assert len(got.shape_names) >= 4
+    assert got.usemtl_names == want.material_names  # name in force at each shape's first face
+
+
+def test_crlf_and_lone_cr_line_endings(tmp_path):
+    body = "v 0 0 0\nv 1 0 0\nv 0 1 0\nvt 0 0\nvn 0 0 1\nf 1/1/1 2/1/1 3/1/1\n"
+    for name, text in [("crlf", body.replace("\n", "\r\n")), ("cr", body.replace("\n", "\r")), ("nofinal", body.rstrip("\n"))]:
+        compare(text, tmp_path, name)
+
+
+def test_unsupported_and_bad_input():
+    with pytest.raises(capi.VkmError) as e:  # pentagon: ear clipping stays on the CPU parser
+        capi.parse_obj(b"v 0 0 0\nv 1 0 0\nv 1 1 0\nv 0 1 0\nv 0.5 2 0\nf 1 2 3 4 5\n")
+    assert e.value.code == 7
+    with pytest.raises(capi.VkmError) as e:  # polyline record
+        capi.parse_obj(b"v 0 0 0\nv 1 0 0\nl 1 2\n")
+    assert e.value.code == 7
+    with pytest.raises(capi.VkmError) as e:  # zero vertex index: tinyobj fails the load
+        capi.parse_obj(b"v 0 0 0\nv 1 0 0\nv 1 1 0\nf 0 1 2\n")
+    assert e.value.code == 2
+    empty = capi.parse_obj(b"")
+    assert len(empty.pos) == 0 and len(empty.idx) == 0 and empty.shape_names == []
+
+
+def test_parse_then_import_equals_reference_loadobj(tmp_path):
+    """OBJ text -> GPU parse -> GPU import == the reference's LoadOBJ on the same file."""
+    from conftest import assert_shapes_equal
+
+    m = synth.concat([synth.uv_sphere(10, 16), synth.grid(12)])
+    p = tmp_path / "mesh.obj"
+    p.write_text(synth.to_obj_text(m))
+    want = refcpu.load_obj(str(p), "mesh")
+    s = capi.parse_obj(p.read_bytes())
+    got = capi.import_shapes(s.pos, s.nrm, s.uv, s.idx, s.shape_offsets)
+    assert_shapes_equal(got, want)
+    assert s.shape_names == [w.name for w in want]

@@ -20,14 +20,14 @@ VERTEX_DTYPE = np.dtype(
 )
 
 VKM_OK = 0
-ERR_NAMES = {1: "INVALID_ARG", 2: "BAD_INDEX", 3: "OOM", 4: "CUDA", 5: "NO_DEVICE", 6: "CAPACITY"}
+ERR_NAMES = {1: "INVALID_ARG", 2: "BAD_INDEX", 3: "OOM", 4: "CUDA", 5: "NO_DEVICE", 6: "CAPACITY", 7: "UNSUPPORTED"}
 
 # every symbol include/vkmesh_b200.h declares (tests check that the library exports all of them)
 SYMBOLS = [
     "vkm_device_count", "vkm_init", "vkm_shutdown", "vkm_last_error", "vkm_version",
     "vkm_generate_tangents", "vkm_generate_normals", "vkm_deduplicate_vertices",
     "vkm_import_shapes", "vkm_free_shape", "vkm_host_alloc", "vkm_host_free",
-    "vkm_e3dm_write", "vkm_e3dm_read", "vkm_e3dm_free",
+    "vkm_e3dm_write", "vkm_e3dm_read", "vkm_e3dm_free", "vkm_parse_obj", "vkm_free_obj_streams",
     "vkm_plan_create", "vkm_plan_destroy", "vkm_plan_import", "vkm_plan_finish", "vkm_plan_set_timing",
     "vkm_plan_phase_name", "vkm_generate_tangents_dev", "vkm_generate_normals_dev",
     "vkm_generate_tangents_dev_noalloc",
@@ -56,6 +56,13 @@ class ShapeOut(C.Structure):
 
 class E3dmConfig(C.Structure):
     _fields_ = [("shape", ShapeOut), ("name", C.c_char_p), ("material_name", C.c_char_p)]
+
+
+class ObjStreams(C.Structure):
+    _fields_ = [("pos", C.POINTER(C.c_float)), ("np", C.c_uint64), ("nrm", C.POINTER(C.c_float)), ("nn", C.c_uint64),
+                ("uv", C.POINTER(C.c_float)), ("nt", C.c_uint64), ("idx_vnt", C.POINTER(C.c_int32)),
+                ("shape_corner_offsets", C.POINTER(C.c_uint64)), ("nshapes", C.c_uint32),
+                ("shape_names", C.POINTER(C.c_char_p)), ("usemtl_names", C.POINTER(C.c_char_p))]
 
 
 class PoolGeometry(C.Structure):
@@ -108,6 +115,9 @@ def lib():
     L.vkm_e3dm_read.restype = C.c_int
     L.vkm_e3dm_read.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.POINTER(E3dmConfig)), C.POINTER(C.c_uint64)]
     L.vkm_e3dm_free.argtypes = [C.POINTER(E3dmConfig), C.c_uint64]
+    L.vkm_parse_obj.restype = C.c_int
+    L.vkm_parse_obj.argtypes = [C.c_int, C.c_char_p, C.c_uint64, C.POINTER(ObjStreams)]
+    L.vkm_free_obj_streams.argtypes = [C.POINTER(ObjStreams)]
     L.vkm_host_alloc.restype = C.c_void_p
     L.vkm_host_alloc.argtypes = [C.c_uint64]
     L.vkm_host_free.argtypes = [C.c_void_p]
@@ -231,6 +241,38 @@ def deduplicate_vertices(vertices: np.ndarray, indices: np.ndarray):
     libc.free.argtypes = [C.c_void_p]
     libc.free(out)  # malloc()ed by the library, as the reference's Platform::AllocMemory result is
     return v, idx
+
+
+@dataclass
+class ParsedObj:
+    pos: np.ndarray
+    nrm: np.ndarray
+    uv: np.ndarray
+    idx: np.ndarray
+    shape_offsets: np.ndarray
+    shape_names: list
+    usemtl_names: list
+
+
+def parse_obj(text: bytes, device: int = 0) -> ParsedObj:
+    """vkm_parse_obj: OBJ text -> tinyobj-shaped streams, parsed on the GPU."""
+    L = lib()
+    s = ObjStreams()
+    _check(L.vkm_parse_obj(device, text, len(text), C.byref(s)))
+    try:
+        ns = s.nshapes
+        ncorners = int(s.shape_corner_offsets[ns]) if ns else 0
+        f = lambda p, n: np.ctypeslib.as_array(p, shape=(n,)).copy() if n else np.empty(0, np.float32)
+        pos = f(s.pos, 3 * s.np).reshape(-1, 3)
+        nrm = f(s.nrm, 3 * s.nn).reshape(-1, 3)
+        uv = f(s.uv, 2 * s.nt).reshape(-1, 2)
+        idx = (np.ctypeslib.as_array(s.idx_vnt, shape=(3 * ncorners,)).copy() if ncorners else np.empty(0, np.int32)).reshape(-1, 3)
+        so = np.array([s.shape_corner_offsets[i] for i in range(ns + 1)], np.uint64)
+        names = [s.shape_names[i].decode() for i in range(ns)]
+        mats = [s.usemtl_names[i].decode() for i in range(ns)]
+        return ParsedObj(pos, nrm, uv, idx, so, names, mats)
+    finally:
+        L.vkm_free_obj_streams(C.byref(s))
 
 
 def e3dm_write(path: str, mesh_name: str, shapes: list, names: list, material_names: list) -> None:

@@ -1,0 +1,684 @@
+// OBJ text parsing on the GPU ("next" row f3).
+//
+// Replaces, for the constructs the engine's assets use, tinyobj::LoadObj as called from
+// MeshLoader::LoadOBJ (mesh_loader.cpp:219; parser: engine/src/vendor/tinyobj/tinyobj.hpp:2557-3115).
+// Output = the same tinyobj-shaped arrays the geometry stage consumes: attrib.vertices / normals / texcoords and
+// the per-shape index_t streams.  Behaviour reproduced from the parser (nothing copied from it):
+//   * lines end at '\n', '\r\n' or a lone '\r' (safeGetline, :762-794); leading blanks are skipped; '#' comments;
+//   * `v x y z ...`, `vn x y z`, `vt u v ...`: numbers are read by the parser's own decimal routine
+//     (tryParseDouble, :890-1020): digits accumulate in a double, fraction digits add digit * 10^-k (a table for
+//     k < 8, pow() beyond), an exponent is applied as ldexp(m * pow(5, e), e), then the double is narrowed to
+//     float.  The two pow() families are tabulated on the HOST with the same libm the CPU parser uses, so the
+//     device reproduces the very same doubles.  Missing numbers default to 0 (parseReal, :1022-1030);
+//   * `f` with 3 or 4 corners in the forms i, i/j, i//k, i/j/k; positive indices are 1-based, negative ones
+//     relative to the records read SO FAR (fixIndex, :815-845), absent vt / vn stay -1; a zero or unresolvable
+//     vertex index fails the load (as tinyobj does);
+//   * quads split along the shorter diagonal, ties -> [0,1,3],[1,2,3] (:1488-1594), float arithmetic;
+//   * `o` / `g` start a new shape; a shape is emitted when it has faces; its name is the o/g text; `usemtl`
+//     does not split shapes -- the name in force at a shape's first face is reported (the engine keeps
+//     material_ids[0], mesh_loader.cpp:231).
+// Not handled on the device (the call returns VKM_ERR_UNSUPPORTED and the caller keeps its CPU parser):
+// polygons with more than 4 corners (ear clipping), `l`, `p`, `vw`, `t` records.
+#include "../../include/vkmesh_b200.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+extern "C" void vkm_internal_set_error(const char* msg);  // vkmesh.cu: feeds vkm_last_error()
+
+namespace {
+
+void perr(const std::string& m) { vkm_internal_set_error(m.c_str()); }
+
+constexpr int kT = 256;
+enum Kind : uint8_t { K_SKIP = 0, K_V, K_VN, K_VT, K_F, K_O, K_G, K_USEMTL, K_BAD };
+
+struct Counts {  // per line, then exclusive prefix
+    uint32_t v, vn, vt, tri, special;
+};
+
+struct ParseStatus {
+    uint32_t unsupported;  // polygon > 4, l / p / vw / t lines
+    uint32_t bad_face;     // zero / unresolvable vertex index
+    uint32_t first_bad_line;
+    uint32_t pad;
+};
+
+__device__ __forceinline__ bool is_space(char c) { return c == ' ' || c == '\t'; }
+__device__ __forceinline__ bool is_digit(char c) { return (unsigned)(c - '0') < 10u; }
+
+// ---- decimal -> double, following tinyobj's routine step by step --------------------------------------------
+__device__ bool try_parse_double(const char* s, const char* s_end, double* result, const double* __restrict__ pow10neg,
+                                 const double* __restrict__ pow5, int pow5_bias) {
+    if (s >= s_end) return false;
+    double mantissa = 0.0;
+    int exponent = 0;
+    char sign = '+', exp_sign = '+';
+    const char* curr = s;
+    int read = 0;
+    bool end_not_reached = false, leading_dot = false;
+    if (*curr == '+' || *curr == '-') {
+        sign = *curr;
+        curr++;
+        if (curr != s_end && *curr == '.') leading_dot = true;
+    } else if (is_digit(*curr)) {
+    } else if (*curr == '.') {
+        leading_dot = true;
+    } else {
+        return false;
+    }
+    end_not_reached = (curr != s_end);
+    if (!leading_dot) {
+        while (end_not_reached && is_digit(*curr)) {
+            mantissa *= 10;
+            mantissa += (int)(*curr - 0x30);
+            curr++;
+            read++;
+            end_not_reached = (curr != s_end);
+        }
+        if (read == 0) return false;
+    }
+    bool have_exp = false;
+    if (end_not_reached) {
+        if (*curr == '.') {
+            curr++;
+            read = 1;
+            end_not_reached = (curr != s_end);
+            while (end_not_reached && is_digit(*curr)) {
+                const double p = read < 400 ? pow10neg[read] : 0.0;  // 10^-400 underflows to 0 in libm as well
+                mantissa += (int)(*curr - 0x30) * p;
+                read++;
+                curr++;
+                end_not_reached = (curr != s_end);
+            }
+            have_exp = end_not_reached && (*curr == 'e' || *curr == 'E');
+        } else if (*curr == 'e' || *curr == 'E') {
+            have_exp = true;
+        }
+    }
+    if (have_exp) {
+        curr++;
+        end_not_reached = (curr != s_end);
+        if (end_not_reached && (*curr == '+' || *curr == '-')) {
+            exp_sign = *curr;
+            curr++;
+        } else if (end_not_reached && is_digit(*curr)) {
+        } else {
+            return false;  // empty exponent
+        }
+        read = 0;
+        end_not_reached = (curr != s_end);
+        while (end_not_reached && is_digit(*curr)) {
+            if (exponent > (2147483647 / 10)) return false;
+            exponent *= 10;
+            exponent += (int)(*curr - 0x30);
+            curr++;
+            read++;
+            end_not_reached = (curr != s_end);
+        }
+        exponent *= (exp_sign == '+' ? 1 : -1);
+        if (read == 0) return false;
+    }
+    double val = mantissa;
+    if (exponent) {
+        double p5;
+        if (exponent < -pow5_bias) p5 = 0.0;                       // pow(5, e) underflows
+        else if (exponent > pow5_bias) p5 = __longlong_as_double(0x7FF0000000000000ll);  // overflows
+        else p5 = pow5[exponent + pow5_bias];
+        val = ldexp(mantissa * p5, exponent);
+    }
+    *result = (sign == '+' ? 1 : -1) * val;
+    return true;
+}
+
+// parseReal: skip blanks, take the token up to blank / '\r', parse, advance.
+__device__ float parse_real(const char*& tok, const char* line_end, const double* p10, const double* p5, int bias) {
+    while (tok < line_end && is_space(*tok)) tok++;
+    const char* end = tok;
+    while (end < line_end && !is_space(*end) && *end != '\r') end++;
+    double val = 0.0;
+    try_parse_double(tok, end, &val, p10, p5, bias);
+    tok = end;
+    return (float)val;
+}
+
+__device__ int parse_int(const char* s, const char* line_end) {  // atoi
+    while (s < line_end && (is_space(*s))) s++;
+    bool neg = false;
+    if (s < line_end && (*s == '+' || *s == '-')) {
+        neg = (*s == '-');
+        s++;
+    }
+    long long v = 0;
+    while (s < line_end && is_digit(*s)) {
+        v = v * 10 + (*s - '0');
+        if (v > 2147483647ll) v = 2147483647ll;
+        s++;
+    }
+    return (int)(neg ? -v : v);
+}
+
+__device__ __forceinline__ bool fix_index(int idx, int n, int* ret, bool allow_zero) {
+    if (idx > 0) {
+        *ret = idx - 1;
+        return true;
+    }
+    if (idx == 0) {
+        *ret = -1;
+        return allow_zero;
+    }
+    *ret = n + idx;
+    return *ret >= 0;
+}
+
+__device__ __forceinline__ const char* skip_to_delim(const char* t, const char* e) {
+    while (t < e && *t != '/' && *t != ' ' && *t != '\t' && *t != '\r') t++;
+    return t;
+}
+
+// parseTriple: i, i/j, i//k, i/j/k
+__device__ bool parse_triple(const char*& tok, const char* e, int nv, int nvn, int nvt, int* v, int* vn, int* vt) {
+    *v = *vn = *vt = -1;
+    if (!fix_index(parse_int(tok, e), nv, v, false)) return false;
+    tok = skip_to_delim(tok, e);
+    if (tok >= e || *tok != '/') return true;
+    tok++;
+    if (tok < e && *tok == '/') {
+        tok++;
+        if (!fix_index(parse_int(tok, e), nvn, vn, true)) return false;
+        tok = skip_to_delim(tok, e);
+        return true;
+    }
+    if (!fix_index(parse_int(tok, e), nvt, vt, true)) return false;
+    tok = skip_to_delim(tok, e);
+    if (tok >= e || *tok != '/') return true;
+    tok++;
+    if (!fix_index(parse_int(tok, e), nvn, vn, true)) return false;
+    tok = skip_to_delim(tok, e);
+    return true;
+}
+
+// ---- kernels ---------------------------------------------------------------------------------------------------
+// bit i of word w set <=> byte 32 w + i starts a line
+__global__ void k_line_bits(const char* __restrict__ text, uint64_t len, uint32_t* bits, uint32_t nwords) {
+    for (uint32_t w = blockIdx.x * blockDim.x + threadIdx.x; w < nwords; w += gridDim.x * blockDim.x) {
+        uint32_t m = 0;
+        const uint64_t base = (uint64_t)w << 5;
+        for (int i = 0; i < 32; ++i) {
+            const uint64_t p = base + i;
+            if (p >= len) break;
+            bool start = (p == 0);
+            if (!start) {
+                const char prev = text[p - 1];
+                // "\r\n" is one terminator: the '\n' right after a '\r' does not start another (empty) line
+                start = (prev == '\n') || (prev == '\r' && text[p] != '\n');
+            }
+            if (start) m |= 1u << i;
+        }
+        bits[w] = m;
+    }
+}
+
+// generic exclusive scan of `n` u32 values per row (rows = blockIdx.y), in place; tile sums in `sums`
+constexpr int kST = 1024, kSI = 4, kSTile = kST * kSI;
+__device__ __forceinline__ uint32_t blk_scan(uint32_t x, uint32_t* total) {
+    __shared__ uint32_t ws[32];
+    const uint32_t lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t inc = x;
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if (lane >= d) inc += y;
+    }
+    if (lane == 31) ws[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t v = ws[lane];
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, v, d);
+            if (lane >= d) v += y;
+        }
+        ws[lane] = v;
+    }
+    __syncthreads();
+    const uint32_t base = wid ? ws[wid - 1] : 0;
+    if (total) *total = ws[31];
+    __syncthreads();
+    return base + inc - x;
+}
+__global__ void __launch_bounds__(kST) k_scan_sum(const uint32_t* data, uint64_t row_stride, uint32_t n, uint32_t* sums,
+                                                 uint32_t ntiles, bool popc) {
+    const uint32_t* d = data + blockIdx.y * row_stride;
+    const uint32_t base = blockIdx.x * kSTile + threadIdx.x * kSI;
+    uint32_t s = 0;
+    for (int i = 0; i < kSI; ++i)
+        if (base + i < n) s += popc ? __popc(d[base + i]) : d[base + i];
+    uint32_t tot;
+    blk_scan(s, &tot);
+    if (threadIdx.x == 0) sums[blockIdx.y * ntiles + blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(kST) k_scan_apply(uint32_t* data, uint64_t row_stride, uint32_t n, const uint32_t* sums,
+                                                   uint32_t ntiles, uint32_t* out, uint64_t out_stride, uint32_t* totals,
+                                                   bool popc) {
+    __shared__ uint32_t red[2][32];
+    const uint32_t* sm = sums + blockIdx.y * ntiles;
+    uint32_t before = 0, all = 0;
+    for (uint32_t i = threadIdx.x; i < ntiles; i += kST) {
+        const uint32_t x = sm[i];
+        all += x;
+        if (i < blockIdx.x) before += x;
+    }
+    for (int d = 16; d; d >>= 1) {
+        before += __shfl_xor_sync(0xFFFFFFFFu, before, d);
+        all += __shfl_xor_sync(0xFFFFFFFFu, all, d);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        red[0][threadIdx.x >> 5] = before;
+        red[1][threadIdx.x >> 5] = all;
+    }
+    __syncthreads();
+    before = all = 0;
+    for (int w = 0; w < kST / 32; ++w) {
+        before += red[0][w];
+        all += red[1][w];
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) totals[blockIdx.y] = all;
+    const uint32_t* d = data + blockIdx.y * row_stride;
+    uint32_t* o = out + blockIdx.y * out_stride;
+    const uint32_t base = blockIdx.x * kSTile + threadIdx.x * kSI;
+    uint32_t x[kSI], s = 0;
+    for (int i = 0; i < kSI; ++i) {
+        x[i] = (base + i < n) ? (popc ? __popc(d[base + i]) : d[base + i]) : 0;
+        s += x[i];
+    }
+    uint32_t run = before + blk_scan(s, nullptr);
+    for (int i = 0; i < kSI; ++i) {
+        if (base + i < n) o[base + i] = run;
+        run += x[i];
+    }
+}
+
+__global__ void k_line_starts(const uint32_t* __restrict__ bits, const uint32_t* __restrict__ prefix, uint32_t nwords,
+                              uint32_t* line_start) {
+    for (uint32_t w = blockIdx.x * blockDim.x + threadIdx.x; w < nwords; w += gridDim.x * blockDim.x) {
+        uint32_t m = bits[w], k = prefix[w];
+        while (m) {
+            const uint32_t b = __ffs(m) - 1;
+            m &= m - 1;
+            line_start[k++] = (w << 5) + b;
+        }
+    }
+}
+
+__device__ __forceinline__ const char* line_end_of(const char* text, uint64_t len, const uint32_t* line_start, uint32_t nlines,
+                                                   uint32_t i) {
+    const char* e = text + ((i + 1 < nlines) ? line_start[i + 1] : len);
+    const char* b = text + line_start[i];
+    while (e > b && (e[-1] == '\n' || e[-1] == '\r')) e--;  // trim the terminator
+    return e;
+}
+
+// rows of `counts`: [0] v, [1] vn, [2] vt, [3] tri, [4] special
+__global__ void k_classify(const char* __restrict__ text, uint64_t len, const uint32_t* __restrict__ line_start,
+                           uint32_t nlines, uint8_t* kind, uint32_t* counts, uint64_t stride, ParseStatus* st) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nlines; i += gridDim.x * blockDim.x) {
+        const char* t = text + line_start[i];
+        const char* e = line_end_of(text, len, line_start, nlines, i);
+        while (t < e && is_space(*t)) t++;
+        uint8_t k = K_SKIP;
+        uint32_t cv = 0, cvn = 0, cvt = 0, ctri = 0, csp = 0;
+        const int n = (int)(e - t);
+        if (n > 0 && t[0] != '#') {
+            const char c1 = n > 1 ? t[1] : '\0', c2 = n > 2 ? t[2] : '\0';
+            if (t[0] == 'v' && is_space(c1)) { k = K_V; cv = 1; }
+            else if (t[0] == 'v' && c1 == 'n' && is_space(c2)) { k = K_VN; cvn = 1; }
+            else if (t[0] == 'v' && c1 == 't' && is_space(c2)) { k = K_VT; cvt = 1; }
+            else if (t[0] == 'v' && c1 == 'w' && is_space(c2)) { k = K_BAD; }
+            else if ((t[0] == 'l' || t[0] == 'p' || t[0] == 't') && is_space(c1)) { k = K_BAD; }
+            else if (t[0] == 'f' && is_space(c1)) {
+                k = K_F;
+                const char* p = t + 2;
+                uint32_t corners = 0;
+                for (;;) {
+                    while (p < e && (is_space(*p) || *p == '\r')) p++;
+                    if (p >= e) break;
+                    corners++;
+                    while (p < e && !is_space(*p) && *p != '\r') p++;
+                }
+                if (corners == 3) ctri = 1;
+                else if (corners == 4) ctri = 2;
+                else if (corners > 4) k = K_BAD;  // ear clipping: left to the CPU parser
+                // fewer than 3: "Degenerated face", dropped
+            } else if (n >= 6 && t[0] == 'u' && t[1] == 's' && t[2] == 'e' && t[3] == 'm' && t[4] == 't' && t[5] == 'l') {
+                k = K_USEMTL; csp = 1;
+            } else if (t[0] == 'g' && is_space(c1)) { k = K_G; csp = 1; }
+            else if (t[0] == 'o' && is_space(c1)) { k = K_O; csp = 1; }
+        }
+        if (k == K_BAD) {
+            st->unsupported = 1;
+            atomicMin(&st->first_bad_line, i);
+        }
+        kind[i] = k;
+        counts[0 * stride + i] = cv;
+        counts[1 * stride + i] = cvn;
+        counts[2 * stride + i] = cvt;
+        counts[3 * stride + i] = ctri;
+        counts[4 * stride + i] = csp;
+    }
+}
+
+__global__ void k_parse_records(const char* __restrict__ text, uint64_t len, const uint32_t* __restrict__ line_start,
+                                uint32_t nlines, const uint8_t* __restrict__ kind, const uint32_t* __restrict__ off,
+                                uint64_t stride, float* pos, float* nrm, float* uv, uint2* special,
+                                const double* __restrict__ p10, const double* __restrict__ p5, int bias) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nlines; i += gridDim.x * blockDim.x) {
+        const uint8_t k = kind[i];
+        if (k == K_SKIP || k == K_F || k == K_BAD) continue;
+        const char* t = text + line_start[i];
+        const char* e = line_end_of(text, len, line_start, nlines, i);
+        while (t < e && is_space(*t)) t++;
+        if (k == K_V) {
+            t += 2;
+            float* d = pos + 3ull * off[0 * stride + i];
+            d[0] = parse_real(t, e, p10, p5, bias);
+            d[1] = parse_real(t, e, p10, p5, bias);
+            d[2] = parse_real(t, e, p10, p5, bias);
+        } else if (k == K_VN) {
+            t += 3;
+            float* d = nrm + 3ull * off[1 * stride + i];
+            d[0] = parse_real(t, e, p10, p5, bias);
+            d[1] = parse_real(t, e, p10, p5, bias);
+            d[2] = parse_real(t, e, p10, p5, bias);
+        } else if (k == K_VT) {
+            t += 3;
+            float* d = uv + 2ull * off[2 * stride + i];
+            d[0] = parse_real(t, e, p10, p5, bias);
+            d[1] = parse_real(t, e, p10, p5, bias);
+        } else {  // o / g / usemtl: (line, triangles before it) for the host-side shape assembly
+            special[off[4 * stride + i]] = make_uint2(line_start[i], off[3 * stride + i]);
+        }
+    }
+}
+
+__global__ void k_parse_faces(const char* __restrict__ text, uint64_t len, const uint32_t* __restrict__ line_start,
+                              uint32_t nlines, const uint8_t* __restrict__ kind, const uint32_t* __restrict__ off,
+                              uint64_t stride, const float* __restrict__ pos, uint32_t np_total, int32_t* idx,
+                              ParseStatus* st) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nlines; i += gridDim.x * blockDim.x) {
+        if (kind[i] != K_F) continue;
+        const char* t = text + line_start[i];
+        const char* e = line_end_of(text, len, line_start, nlines, i);
+        while (t < e && is_space(*t)) t++;
+        t += 2;
+        while (t < e && is_space(*t)) t++;
+        const int nv = (int)off[0 * stride + i], nvn = (int)off[1 * stride + i], nvt = (int)off[2 * stride + i];
+        int cv[4], cn[4], ct[4];
+        int corners = 0;
+        bool ok = true;
+        while (t < e && *t != '\r' && corners < 4) {
+            if (!parse_triple(t, e, nv, nvn, nvt, &cv[corners], &cn[corners], &ct[corners])) {
+                ok = false;
+                break;
+            }
+            corners++;
+            while (t < e && (is_space(*t) || *t == '\r')) t++;
+        }
+        if (!ok) {  // tinyobj fails the whole load here
+            st->bad_face = 1;
+            atomicMin(&st->first_bad_line, i);
+            continue;
+        }
+        if (corners < 3) continue;
+        int32_t* out = idx + 9ull * off[3 * stride + i];
+        int order[6] = {0, 1, 2, 0, 2, 3};
+        if (corners == 4) {
+            // the parser reads positions through indices that must already be valid when the group is exported;
+            // here: valid in the finished array (a forward reference past the export point would differ: not handled)
+            bool valid = true;
+            for (int q = 0; q < 4; ++q) valid &= (cv[q] >= 0 && (uint32_t)cv[q] < np_total);
+            if (!valid) {  // "Face with invalid vertex index found": tinyobj drops the quad, counted as 2 triangles here
+                st->bad_face = 1;
+                atomicMin(&st->first_bad_line, i);
+                continue;
+            }
+            const float* p0 = pos + 3ull * cv[0];
+            const float* p1 = pos + 3ull * cv[1];
+            const float* p2 = pos + 3ull * cv[2];
+            const float* p3 = pos + 3ull * cv[3];
+            const float ax = __fsub_rn(p2[0], p0[0]), ay = __fsub_rn(p2[1], p0[1]), az = __fsub_rn(p2[2], p0[2]);
+            const float bx = __fsub_rn(p3[0], p1[0]), by = __fsub_rn(p3[1], p1[1]), bz = __fsub_rn(p3[2], p1[2]);
+            const float s02 = __fadd_rn(__fadd_rn(__fmul_rn(ax, ax), __fmul_rn(ay, ay)), __fmul_rn(az, az));
+            const float s13 = __fadd_rn(__fadd_rn(__fmul_rn(bx, bx), __fmul_rn(by, by)), __fmul_rn(bz, bz));
+            if (!(s02 < s13)) {  // [0,1,3],[1,2,3]
+                order[2] = 3; order[3] = 1; order[4] = 2; order[5] = 3;
+            }
+        }
+        const int ntri = corners == 4 ? 2 : 1;
+        for (int q = 0; q < 3 * ntri; ++q) {
+            out[3 * q + 0] = cv[order[q]];
+            out[3 * q + 1] = cn[order[q]];
+            out[3 * q + 2] = ct[order[q]];
+        }
+    }
+}
+
+#define PCU(call)                                                                       \
+    do {                                                                                \
+        cudaError_t e_ = (call);                                                        \
+        if (e_ != cudaSuccess) {                                                        \
+            perr(std::string(#call) + " failed: " + cudaGetErrorString(e_));            \
+            rc = (e_ == cudaErrorMemoryAllocation) ? VKM_ERR_OOM : VKM_ERR_CUDA;        \
+            goto done;                                                                  \
+        }                                                                               \
+    } while (0)
+
+unsigned grid_of(uint64_t n) { return (unsigned)std::max<uint64_t>(1, std::min<uint64_t>((n + kT - 1) / kT, 148 * 8)); }
+
+}  // namespace
+
+extern "C" {
+
+void vkm_free_obj_streams(vkm_obj_streams* s) {
+    if (!s) return;
+    free(s->pos); free(s->nrm); free(s->uv); free(s->idx_vnt); free(s->shape_corner_offsets);
+    for (uint32_t i = 0; i < s->nshapes; ++i) {
+        if (s->shape_names) free(s->shape_names[i]);
+        if (s->usemtl_names) free(s->usemtl_names[i]);
+    }
+    free(s->shape_names); free(s->usemtl_names);
+    memset(s, 0, sizeof *s);
+}
+
+int vkm_parse_obj(int device, const char* text, uint64_t len, vkm_obj_streams* out) {
+    if (!text || !out) return VKM_ERR_INVALID_ARG;
+    memset(out, 0, sizeof *out);
+    if (len >= 0xFFFFFF00ull) { perr("OBJ text beyond 4 GiB"); return VKM_ERR_INVALID_ARG; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device >= ndev) {
+        cudaGetLastError();
+        perr("no CUDA device (there is no CPU path)");
+        return VKM_ERR_NO_DEVICE;
+    }
+    int rc = VKM_OK;
+    // pow tables from the host libm: the same doubles tinyobj's std::pow calls produce on this machine
+    constexpr int kP10 = 400, kBias = 1100;
+    std::vector<double> h_p10(kP10), h_p5(2 * kBias + 1);
+    static const double lut[8] = {1.0, 0.1, 0.01, 0.001, 0.0001, 0.00001, 0.000001, 0.0000001};
+    for (int k = 0; k < kP10; ++k) h_p10[k] = k < 8 ? lut[k] : std::pow(10.0, -k);
+    for (int e = -kBias; e <= kBias; ++e) h_p5[e + kBias] = std::pow(5.0, e);
+
+    char* d_text = nullptr;
+    uint32_t *d_bits = nullptr, *d_bpre = nullptr, *d_sums = nullptr, *d_tot = nullptr, *d_ls = nullptr, *d_cnt = nullptr,
+             *d_off = nullptr;
+    uint8_t* d_kind = nullptr;
+    double *d_p10 = nullptr, *d_p5 = nullptr;
+    float *d_pos = nullptr, *d_nrm = nullptr, *d_uv = nullptr;
+    int32_t* d_idx = nullptr;
+    uint2* d_sp = nullptr;
+    ParseStatus* d_st = nullptr;
+    ParseStatus hst{};
+    uint32_t tot[5] = {0, 0, 0, 0, 0};
+    uint32_t nlines = 0;
+    std::vector<uint2> special;
+    const uint32_t nwords = (uint32_t)((len + 31) / 32);
+    const uint32_t nt1 = std::max<uint32_t>(1, (nwords + kSTile - 1) / kSTile);
+    cudaStream_t st = nullptr;
+
+    PCU(cudaSetDevice(device));
+    PCU(cudaMalloc(&d_text, len + 1));
+    PCU(cudaMalloc(&d_bits, (uint64_t)(nwords + 1) * 4));
+    PCU(cudaMalloc(&d_bpre, (uint64_t)(nwords + 1) * 4));
+    PCU(cudaMalloc(&d_sums, (uint64_t)nt1 * 4 + 64));
+    PCU(cudaMalloc(&d_tot, 64));
+    PCU(cudaMalloc(&d_p10, sizeof(double) * kP10));
+    PCU(cudaMalloc(&d_p5, sizeof(double) * (2 * kBias + 1)));
+    PCU(cudaMalloc(&d_st, sizeof(ParseStatus)));
+    PCU(cudaMemcpyAsync(d_text, text, len, cudaMemcpyHostToDevice, st));
+    PCU(cudaMemcpyAsync(d_p10, h_p10.data(), sizeof(double) * kP10, cudaMemcpyHostToDevice, st));
+    PCU(cudaMemcpyAsync(d_p5, h_p5.data(), sizeof(double) * (2 * kBias + 1), cudaMemcpyHostToDevice, st));
+    hst.first_bad_line = 0xFFFFFFFFu;
+    PCU(cudaMemcpyAsync(d_st, &hst, sizeof hst, cudaMemcpyHostToDevice, st));
+    if (len) {
+        k_line_bits<<<grid_of(nwords), kT, 0, st>>>(d_text, len, d_bits, nwords);
+        k_scan_sum<<<dim3(nt1, 1), kST, 0, st>>>(d_bits, 0, nwords, d_sums, nt1, true);
+        k_scan_apply<<<dim3(nt1, 1), kST, 0, st>>>(d_bits, 0, nwords, d_sums, nt1, d_bpre, 0, d_tot, true);
+        PCU(cudaMemcpyAsync(&nlines, d_tot, 4, cudaMemcpyDeviceToHost, st));
+        PCU(cudaStreamSynchronize(st));
+    }
+    if (nlines) {
+        const uint64_t L = nlines;
+        const uint32_t nt2 = std::max<uint32_t>(1, (nlines + kSTile - 1) / kSTile);
+        PCU(cudaMalloc(&d_ls, L * 4));
+        PCU(cudaMalloc(&d_kind, L));
+        PCU(cudaMalloc(&d_cnt, L * 4 * 5));
+        PCU(cudaMalloc(&d_off, L * 4 * 5));
+        cudaFree(d_sums);
+        d_sums = nullptr;
+        PCU(cudaMalloc(&d_sums, (uint64_t)nt2 * 4 * 5 + 64));
+        k_line_starts<<<grid_of(nwords), kT, 0, st>>>(d_bits, d_bpre, nwords, d_ls);
+        k_classify<<<grid_of(nlines), kT, 0, st>>>(d_text, len, d_ls, nlines, d_kind, d_cnt, L, d_st);
+        k_scan_sum<<<dim3(nt2, 5), kST, 0, st>>>(d_cnt, L, nlines, d_sums, nt2, false);
+        k_scan_apply<<<dim3(nt2, 5), kST, 0, st>>>(d_cnt, L, nlines, d_sums, nt2, d_off, L, d_tot, false);
+        PCU(cudaMemcpyAsync(tot, d_tot, 20, cudaMemcpyDeviceToHost, st));
+        PCU(cudaMemcpyAsync(&hst, d_st, sizeof hst, cudaMemcpyDeviceToHost, st));
+        PCU(cudaStreamSynchronize(st));
+        if (hst.unsupported) {
+            perr("line " + std::to_string(hst.first_bad_line + 1) + ": construct left to the CPU parser (polygon with more than 4 corners, l / p / vw / t record)");
+            rc = VKM_ERR_UNSUPPORTED;
+            goto done;
+        }
+        PCU(cudaMalloc(&d_pos, std::max<uint64_t>(1, (uint64_t)tot[0] * 12)));
+        PCU(cudaMalloc(&d_nrm, std::max<uint64_t>(1, (uint64_t)tot[1] * 12)));
+        PCU(cudaMalloc(&d_uv, std::max<uint64_t>(1, (uint64_t)tot[2] * 8)));
+        PCU(cudaMalloc(&d_idx, std::max<uint64_t>(1, (uint64_t)tot[3] * 36)));
+        PCU(cudaMalloc(&d_sp, std::max<uint64_t>(1, (uint64_t)tot[4] * 8)));
+        k_parse_records<<<grid_of(nlines), kT, 0, st>>>(d_text, len, d_ls, nlines, d_kind, d_off, L, d_pos, d_nrm, d_uv, d_sp,
+                                                        d_p10, d_p5, kBias);
+        k_parse_faces<<<grid_of(nlines), kT, 0, st>>>(d_text, len, d_ls, nlines, d_kind, d_off, L, d_pos, tot[0], d_idx, d_st);
+        PCU(cudaGetLastError());
+        PCU(cudaMemcpyAsync(&hst, d_st, sizeof hst, cudaMemcpyDeviceToHost, st));
+        special.resize(tot[4]);
+        if (tot[4]) PCU(cudaMemcpyAsync(special.data(), d_sp, (uint64_t)tot[4] * 8, cudaMemcpyDeviceToHost, st));
+        PCU(cudaStreamSynchronize(st));
+        if (hst.bad_face) {
+            perr("line " + std::to_string(hst.first_bad_line + 1) + ": face with a zero or unresolvable vertex index (tinyobj fails the load here)");
+            rc = VKM_ERR_BAD_INDEX;
+            goto done;
+        }
+    }
+    {
+        out->np = tot[0]; out->nn = tot[1]; out->nt = tot[2];
+        out->pos = (float*)malloc(std::max<uint64_t>(1, (uint64_t)tot[0] * 12));
+        out->nrm = (float*)malloc(std::max<uint64_t>(1, (uint64_t)tot[1] * 12));
+        out->uv = (float*)malloc(std::max<uint64_t>(1, (uint64_t)tot[2] * 8));
+        out->idx_vnt = (int32_t*)malloc(std::max<uint64_t>(1, (uint64_t)tot[3] * 36));
+        if (!out->pos || !out->nrm || !out->uv || !out->idx_vnt) { rc = VKM_ERR_OOM; perr("host allocation failed"); goto done; }
+        if (tot[0]) PCU(cudaMemcpyAsync(out->pos, d_pos, (uint64_t)tot[0] * 12, cudaMemcpyDeviceToHost, st));
+        if (tot[1]) PCU(cudaMemcpyAsync(out->nrm, d_nrm, (uint64_t)tot[1] * 12, cudaMemcpyDeviceToHost, st));
+        if (tot[2]) PCU(cudaMemcpyAsync(out->uv, d_uv, (uint64_t)tot[2] * 8, cudaMemcpyDeviceToHost, st));
+        if (tot[3]) PCU(cudaMemcpyAsync(out->idx_vnt, d_idx, (uint64_t)tot[3] * 36, cudaMemcpyDeviceToHost, st));
+        PCU(cudaStreamSynchronize(st));
+        // ---- shapes (host; the o / g / usemtl lines are few): a shape = the faces between two o/g lines
+        auto line_text = [&](uint32_t line_start_byte) {
+            const char* b = text + line_start_byte;
+            const char* e = b;
+            while (e < text + len && *e != '\n' && *e != '\r') e++;
+            while (b < e && (*b == ' ' || *b == '\t')) b++;
+            return std::string(b, e);
+        };
+        std::vector<uint64_t> offs{0};
+        std::vector<std::string> names, mats;
+        std::string cur_name, cur_mat, seg_mat;
+        uint32_t seg_start = 0;
+        bool seg_mat_fixed = false;
+        auto close_segment = [&](uint32_t tri_end) {
+            if (tri_end > seg_start) {
+                offs.push_back((uint64_t)tri_end * 3);
+                names.push_back(cur_name);
+                mats.push_back(seg_mat_fixed ? seg_mat : cur_mat);
+            }
+            seg_start = tri_end;
+            seg_mat_fixed = false;
+        };
+        for (size_t k = 0; k < special.size(); ++k) {
+            const std::string ln = line_text(special[k].x);
+            const uint32_t tri_at = special[k].y;
+            if (tri_at > seg_start && !seg_mat_fixed) {  // the segment already has faces: its material is settled
+                seg_mat = cur_mat;
+                seg_mat_fixed = true;
+            }
+            if (ln.compare(0, 6, "usemtl") == 0) {
+                size_t b = 6;
+                while (b < ln.size() && (ln[b] == ' ' || ln[b] == '\t')) b++;
+                size_t e = b;
+                while (e < ln.size() && ln[e] != ' ' && ln[e] != '\t' && ln[e] != '\r') e++;
+                cur_mat = ln.substr(b, e - b);
+            } else if (ln[0] == 'o') {
+                close_segment(tri_at);
+                cur_name = ln.size() > 2 ? ln.substr(2) : std::string();
+            } else {  // g: names joined by single blanks
+                close_segment(tri_at);
+                std::string nm;
+                size_t p = 1;
+                bool first = true;
+                while (p < ln.size()) {
+                    while (p < ln.size() && (ln[p] == ' ' || ln[p] == '\t' || ln[p] == '\r')) p++;
+                    size_t e = p;
+                    while (e < ln.size() && ln[e] != ' ' && ln[e] != '\t' && ln[e] != '\r') e++;
+                    if (e > p) {
+                        if (!first) nm += " ";
+                        nm += ln.substr(p, e - p);
+                        first = false;
+                    }
+                    p = e;
+                }
+                cur_name = nm;
+            }
+        }
+        if (tot[3] > seg_start && !seg_mat_fixed) { seg_mat = cur_mat; seg_mat_fixed = true; }
+        close_segment(tot[3]);
+        out->nshapes = (uint32_t)names.size();
+        out->shape_corner_offsets = (uint64_t*)malloc(sizeof(uint64_t) * offs.size());
+        out->shape_names = (char**)calloc(std::max<size_t>(1, names.size()), sizeof(char*));
+        out->usemtl_names = (char**)calloc(std::max<size_t>(1, names.size()), sizeof(char*));
+        if (!out->shape_corner_offsets || !out->shape_names || !out->usemtl_names) { rc = VKM_ERR_OOM; goto done; }
+        memcpy(out->shape_corner_offsets, offs.data(), sizeof(uint64_t) * offs.size());
+        for (size_t k = 0; k < names.size(); ++k) {
+            out->shape_names[k] = strdup(names[k].c_str());
+            out->usemtl_names[k] = strdup(mats[k].c_str());
+        }
+    }
+done:
+    cudaFree(d_text); cudaFree(d_bits); cudaFree(d_bpre); cudaFree(d_sums); cudaFree(d_tot); cudaFree(d_ls);
+    cudaFree(d_cnt); cudaFree(d_off); cudaFree(d_kind); cudaFree(d_p10); cudaFree(d_p5); cudaFree(d_pos);
+    cudaFree(d_nrm); cudaFree(d_uv); cudaFree(d_idx); cudaFree(d_sp); cudaFree(d_st);
+    if (rc != VKM_OK) vkm_free_obj_streams(out);
+    return rc;
+}
+
+}  // extern "C"

@@ -293,6 +293,7 @@ int plan_enqueue(vkm_plan* p) {
 extern "C" {
 
 const char* vkm_last_error(void) { return g_err.c_str(); }
+void vkm_internal_set_error(const char* msg) { g_err = msg ? msg : ""; }  // for the library's other translation units
 const char* vkm_version(void) { return "vkmesh_b200 0.1 (sm_100a)"; }
 
 int vkm_device_count(void) {
