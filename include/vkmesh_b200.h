@@ -115,6 +115,18 @@ typedef struct vkm_obj_streams {
 int vkm_parse_obj(int device, const char* text, uint64_t len, vkm_obj_streams* out);
 void vkm_free_obj_streams(vkm_obj_streams* streams);
 
+/* The whole of MeshLoader::LoadOBJ (mesh_loader.cpp:200-328) from OBJ text: parse on the GPU, run the geometry
+ * stage on the device-resident streams (they never visit the host), return GeometryConfig-shaped buffers
+ * (malloc()ed) with shape names.  Same restrictions as vkm_parse_obj. */
+typedef struct vkm_obj_import {
+    uint32_t nshapes;
+    vkm_shape_out* shapes;
+    char** shape_names;
+    char** usemtl_names;
+} vkm_obj_import;
+int vkm_import_obj_text(int device, const char* text, uint64_t len, vkm_obj_import* out);
+void vkm_free_obj_import(vkm_obj_import* result);
+
 /* ---- E3DM import cache: replaces b8 MeshLoader::WriteToE3DM(const std::string&, const std::string&,
  *      GeometryConfigs&) and MeshResource* MeshLoader::LoadE3DM(const std::string&, const std::string&)
  *      -- mesh_loader.cpp:63-126 and :128-198.  Host-side file code; byte-compatible with the reference's files. ---- */

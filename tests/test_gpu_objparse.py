@@ -143,3 +143,18 @@ def test_parse_then_import_equals_reference_loadobj(tmp_path):
     got = capi.import_shapes(s.pos, s.nrm, s.uv, s.idx, s.shape_offsets)
     assert_shapes_equal(got, want)
     assert s.shape_names == [w.name for w in want]
+
+
+def test_import_obj_text_equals_reference_loadobj(tmp_path):
+    """The whole of LoadOBJ from text on the GPU (streams never visit the host) == the reference on the same file."""
+    from conftest import assert_shapes_equal
+
+    (tmp_path / "tricky.mtl").write_text("newmtl matA\nKd 1 0 0\nnewmtl matB\nKd 0 1 0\n")
+    m = synth.concat([synth.uv_sphere(9, 14), synth.grid(11), synth.adversarial(10)])
+    for name, text in [("mesh", synth.to_obj_text(m))]:
+        p = tmp_path / (name + ".obj")
+        p.write_text(text)
+        want = refcpu.load_obj(str(p), name)
+        got, names, mats = capi.import_obj_text(text.encode())
+        assert_shapes_equal(got, want)
+        assert names == [w.name for w in want]

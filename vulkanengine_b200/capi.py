@@ -28,6 +28,7 @@ SYMBOLS = [
     "vkm_generate_tangents", "vkm_generate_normals", "vkm_deduplicate_vertices",
     "vkm_import_shapes", "vkm_free_shape", "vkm_host_alloc", "vkm_host_free",
     "vkm_e3dm_write", "vkm_e3dm_read", "vkm_e3dm_free", "vkm_parse_obj", "vkm_free_obj_streams",
+    "vkm_import_obj_text", "vkm_free_obj_import",
     "vkm_plan_create", "vkm_plan_destroy", "vkm_plan_import", "vkm_plan_finish", "vkm_plan_set_timing",
     "vkm_plan_phase_name", "vkm_generate_tangents_dev", "vkm_generate_normals_dev",
     "vkm_generate_tangents_dev_noalloc",
@@ -63,6 +64,11 @@ class ObjStreams(C.Structure):
                 ("uv", C.POINTER(C.c_float)), ("nt", C.c_uint64), ("idx_vnt", C.POINTER(C.c_int32)),
                 ("shape_corner_offsets", C.POINTER(C.c_uint64)), ("nshapes", C.c_uint32),
                 ("shape_names", C.POINTER(C.c_char_p)), ("usemtl_names", C.POINTER(C.c_char_p))]
+
+
+class ObjImport(C.Structure):
+    _fields_ = [("nshapes", C.c_uint32), ("shapes", C.POINTER(ShapeOut)), ("shape_names", C.POINTER(C.c_char_p)),
+                ("usemtl_names", C.POINTER(C.c_char_p))]
 
 
 class PoolGeometry(C.Structure):
@@ -118,6 +124,9 @@ def lib():
     L.vkm_parse_obj.restype = C.c_int
     L.vkm_parse_obj.argtypes = [C.c_int, C.c_char_p, C.c_uint64, C.POINTER(ObjStreams)]
     L.vkm_free_obj_streams.argtypes = [C.POINTER(ObjStreams)]
+    L.vkm_import_obj_text.restype = C.c_int
+    L.vkm_import_obj_text.argtypes = [C.c_int, C.c_char_p, C.c_uint64, C.POINTER(ObjImport)]
+    L.vkm_free_obj_import.argtypes = [C.POINTER(ObjImport)]
     L.vkm_host_alloc.restype = C.c_void_p
     L.vkm_host_alloc.argtypes = [C.c_uint64]
     L.vkm_host_free.argtypes = [C.c_void_p]
@@ -273,6 +282,25 @@ def parse_obj(text: bytes, device: int = 0) -> ParsedObj:
         return ParsedObj(pos, nrm, uv, idx, so, names, mats)
     finally:
         L.vkm_free_obj_streams(C.byref(s))
+
+
+def import_obj_text(text: bytes, device: int = 0):
+    """vkm_import_obj_text: OBJ text -> finished shapes, all on the GPU.  Returns (shapes, names, usemtl names)."""
+    L = lib()
+    r = ObjImport()
+    _check(L.vkm_import_obj_text(device, text, len(text), C.byref(r)))
+    try:
+        shapes, names, mats = [], [], []
+        for i in range(r.nshapes):
+            o = r.shapes[i]
+            e = np.array(list(o.extent.center) + list(o.extent.min_extents) + list(o.extent.max_extents), np.float32)
+            shapes.append(ShapeResult(_copy_out(o.vertices, 64 * o.vertex_count, VERTEX_DTYPE),
+                                      _copy_out(o.indices, 4 * o.index_count, np.uint32), e))
+            names.append(r.shape_names[i].decode())
+            mats.append(r.usemtl_names[i].decode())
+        return shapes, names, mats
+    finally:
+        L.vkm_free_obj_import(C.byref(r))
 
 
 def e3dm_write(path: str, mesh_name: str, shapes: list, names: list, material_names: list) -> None:

@@ -31,6 +31,9 @@
 #include <vector>
 
 extern "C" void vkm_internal_set_error(const char* msg);  // vkmesh.cu: feeds vkm_last_error()
+extern "C" int vkm_internal_import_device(int device, const float* d_pos, uint64_t np, const float* d_nrm, uint64_t nn,
+                                          const float* d_uv, uint64_t nt, const int32_t* d_idx, const uint64_t* shape_off,
+                                          uint32_t nshapes, vkm_shape_out* out);
 
 namespace {
 
@@ -494,7 +497,9 @@ void vkm_free_obj_streams(vkm_obj_streams* s) {
     memset(s, 0, sizeof *s);
 }
 
-int vkm_parse_obj(int device, const char* text, uint64_t len, vkm_obj_streams* out) {
+// Shared body: `imp == nullptr` -> return the streams in `out`; otherwise keep the streams on the device, run the
+// geometry stage on them and return finished shapes in `imp` (names in both cases).
+static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_streams* out, vkm_obj_import* imp) {
     if (!text || !out) return VKM_ERR_INVALID_ARG;
     memset(out, 0, sizeof *out);
     if (len >= 0xFFFFFF00ull) { perr("OBJ text beyond 4 GiB"); return VKM_ERR_INVALID_ARG; }
@@ -593,15 +598,17 @@ int vkm_parse_obj(int device, const char* text, uint64_t len, vkm_obj_streams* o
     }
     {
         out->np = tot[0]; out->nn = tot[1]; out->nt = tot[2];
-        out->pos = (float*)malloc(std::max<uint64_t>(1, (uint64_t)tot[0] * 12));
-        out->nrm = (float*)malloc(std::max<uint64_t>(1, (uint64_t)tot[1] * 12));
-        out->uv = (float*)malloc(std::max<uint64_t>(1, (uint64_t)tot[2] * 8));
-        out->idx_vnt = (int32_t*)malloc(std::max<uint64_t>(1, (uint64_t)tot[3] * 36));
-        if (!out->pos || !out->nrm || !out->uv || !out->idx_vnt) { rc = VKM_ERR_OOM; perr("host allocation failed"); goto done; }
-        if (tot[0]) PCU(cudaMemcpyAsync(out->pos, d_pos, (uint64_t)tot[0] * 12, cudaMemcpyDeviceToHost, st));
-        if (tot[1]) PCU(cudaMemcpyAsync(out->nrm, d_nrm, (uint64_t)tot[1] * 12, cudaMemcpyDeviceToHost, st));
-        if (tot[2]) PCU(cudaMemcpyAsync(out->uv, d_uv, (uint64_t)tot[2] * 8, cudaMemcpyDeviceToHost, st));
-        if (tot[3]) PCU(cudaMemcpyAsync(out->idx_vnt, d_idx, (uint64_t)tot[3] * 36, cudaMemcpyDeviceToHost, st));
+        if (!imp) {
+            out->pos = (float*)malloc(std::max<uint64_t>(1, (uint64_t)tot[0] * 12));
+            out->nrm = (float*)malloc(std::max<uint64_t>(1, (uint64_t)tot[1] * 12));
+            out->uv = (float*)malloc(std::max<uint64_t>(1, (uint64_t)tot[2] * 8));
+            out->idx_vnt = (int32_t*)malloc(std::max<uint64_t>(1, (uint64_t)tot[3] * 36));
+            if (!out->pos || !out->nrm || !out->uv || !out->idx_vnt) { rc = VKM_ERR_OOM; perr("host allocation failed"); goto done; }
+            if (tot[0]) PCU(cudaMemcpyAsync(out->pos, d_pos, (uint64_t)tot[0] * 12, cudaMemcpyDeviceToHost, st));
+            if (tot[1]) PCU(cudaMemcpyAsync(out->nrm, d_nrm, (uint64_t)tot[1] * 12, cudaMemcpyDeviceToHost, st));
+            if (tot[2]) PCU(cudaMemcpyAsync(out->uv, d_uv, (uint64_t)tot[2] * 8, cudaMemcpyDeviceToHost, st));
+            if (tot[3]) PCU(cudaMemcpyAsync(out->idx_vnt, d_idx, (uint64_t)tot[3] * 36, cudaMemcpyDeviceToHost, st));
+        }
         PCU(cudaStreamSynchronize(st));
         // ---- shapes (host; the o / g / usemtl lines are few): a shape = the faces between two o/g lines
         auto line_text = [&](uint32_t line_start_byte) {
@@ -672,6 +679,13 @@ int vkm_parse_obj(int device, const char* text, uint64_t len, vkm_obj_streams* o
             out->shape_names[k] = strdup(names[k].c_str());
             out->usemtl_names[k] = strdup(mats[k].c_str());
         }
+        if (imp && out->nshapes) {  // geometry stage straight from the device-resident streams
+            imp->shapes = (vkm_shape_out*)calloc(out->nshapes, sizeof(vkm_shape_out));
+            if (!imp->shapes) { rc = VKM_ERR_OOM; perr("host allocation failed"); goto done; }
+            rc = vkm_internal_import_device(device, d_pos, tot[0], d_nrm, tot[1], d_uv, tot[2], d_idx,
+                                            out->shape_corner_offsets, out->nshapes, imp->shapes);
+            if (rc != VKM_OK) { free(imp->shapes); imp->shapes = nullptr; goto done; }
+        }
     }
 done:
     cudaFree(d_text); cudaFree(d_bits); cudaFree(d_bpre); cudaFree(d_sums); cudaFree(d_tot); cudaFree(d_ls);
@@ -679,6 +693,36 @@ done:
     cudaFree(d_nrm); cudaFree(d_uv); cudaFree(d_idx); cudaFree(d_sp); cudaFree(d_st);
     if (rc != VKM_OK) vkm_free_obj_streams(out);
     return rc;
+}
+
+int vkm_parse_obj(int device, const char* text, uint64_t len, vkm_obj_streams* out) {
+    return parse_impl(device, text, len, out, nullptr);
+}
+
+void vkm_free_obj_import(vkm_obj_import* r) {
+    if (!r) return;
+    for (uint32_t i = 0; i < r->nshapes; ++i) {
+        if (r->shapes) vkm_free_shape(&r->shapes[i]);
+        if (r->shape_names) free(r->shape_names[i]);
+        if (r->usemtl_names) free(r->usemtl_names[i]);
+    }
+    free(r->shapes); free(r->shape_names); free(r->usemtl_names);
+    memset(r, 0, sizeof *r);
+}
+
+int vkm_import_obj_text(int device, const char* text, uint64_t len, vkm_obj_import* out) {
+    if (!out) return VKM_ERR_INVALID_ARG;
+    memset(out, 0, sizeof *out);
+    vkm_obj_streams s;
+    const int rc = parse_impl(device, text, len, &s, out);
+    if (rc != VKM_OK) return rc;
+    out->nshapes = s.nshapes;  // hand the name arrays over, drop the rest
+    out->shape_names = s.shape_names;
+    out->usemtl_names = s.usemtl_names;
+    s.shape_names = s.usemtl_names = nullptr;
+    s.nshapes = 0;
+    vkm_free_obj_streams(&s);
+    return VKM_OK;
 }
 
 }  // extern "C"

@@ -824,23 +824,13 @@ void vkm_free_shape(vkm_shape_out* s) {
     s->indices = nullptr;
 }
 
-int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t nn, const float* uv, uint64_t nt,
-                      const int32_t* idx, const uint64_t* shape_off, uint32_t nshapes, vkm_shape_out* out) {
-    if (nshapes == 0) return VKM_OK;
-    if (!shape_off || !out) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: null argument");
-    for (uint32_t s = 0; s < nshapes; ++s) {
-        memset(&out[s], 0, sizeof(vkm_shape_out));
-        out[s].vertex_size = 64;
-        out[s].index_size = 4;
-    }
+// The part of the host entry point that runs once the streams are in device memory: plan, kernels, results into
+// malloc()ed buffers.  Caller holds g_ctx.mu and has bound the context.
+static int import_resident(HostCtx& c, const float* d_pos, uint64_t np, const float* d_nrm, uint64_t nn, const float* d_uv,
+                           uint64_t nt, const int32_t* d_idx, const uint64_t* shape_off, uint32_t nshapes,
+                           vkm_shape_out* out, Trace& tr) {
+    int rc;
     const uint64_t C = shape_off[nshapes];
-    if (C > kMaxCorners) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: too many corners");
-    if (C > 0 && (!pos || !nrm || !uv || !idx)) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: null input stream");
-    std::lock_guard<std::mutex> lk(g_ctx.mu);
-    HostCtx& c = g_ctx;
-    Trace tr;
-    int rc = ctx_bind(c);
-    if (rc) return rc;
     const uint64_t max_attrib = std::max(np, std::max(nn, nt));
     if (!c.plan || c.plan->desc.max_corners < C || c.plan->desc.max_shapes < nshapes || c.plan->desc.max_attrib < max_attrib) {
         if (c.plan) vkm_plan_destroy(c.plan);
@@ -853,17 +843,8 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
         d.max_shapes = nshapes;
         if ((rc = vkm_plan_create(&d, &c.plan))) return rc;
     }
-    if ((rc = c.pos.ensure(3 * np + 4))) return rc;
-    if ((rc = c.nrm.ensure(3 * nn + 4))) return rc;
-    if ((rc = c.uv.ensure(2 * nt + 4))) return rc;
-    if ((rc = c.idx.ensure(3 * C + 16))) return rc;
-    if (np) CU(cudaMemcpyAsync(c.pos.p, pos, np * 12, cudaMemcpyHostToDevice, c.st));
-    if (nn) CU(cudaMemcpyAsync(c.nrm.p, nrm, nn * 12, cudaMemcpyHostToDevice, c.st));
-    if (nt) CU(cudaMemcpyAsync(c.uv.p, uv, nt * 8, cudaMemcpyHostToDevice, c.st));
-    if (C) CU(cudaMemcpyAsync(c.idx.p, idx, C * 12, cudaMemcpyHostToDevice, c.st));
-    tr.mark("enqueue H2D");
     c.plan->t1_mode = 0;  // every host call is a new mesh: try the coherent addressing first
-    if ((rc = vkm_plan_import(c.plan, c.pos.p, np, c.nrm.p, nn, c.uv.p, nt, c.idx.p, shape_off, nshapes, c.st))) return rc;
+    if ((rc = vkm_plan_import(c.plan, d_pos, np, d_nrm, nn, d_uv, nt, d_idx, shape_off, nshapes, c.st))) return rc;
     vkm_plan_result r{};
     if ((rc = vkm_plan_finish(c.plan, &r))) return rc;
     tr.mark("H2D + kernels (finish)");
@@ -894,6 +875,55 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
     }
     tr.mark("D2H + copy-out");
     return VKM_OK;
+}
+
+static void init_shape_outs(vkm_shape_out* out, uint32_t nshapes) {
+    for (uint32_t s = 0; s < nshapes; ++s) {
+        memset(&out[s], 0, sizeof(vkm_shape_out));
+        out[s].vertex_size = 64;
+        out[s].index_size = 4;
+    }
+}
+
+int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t nn, const float* uv, uint64_t nt,
+                      const int32_t* idx, const uint64_t* shape_off, uint32_t nshapes, vkm_shape_out* out) {
+    if (nshapes == 0) return VKM_OK;
+    if (!shape_off || !out) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: null argument");
+    init_shape_outs(out, nshapes);
+    const uint64_t C = shape_off[nshapes];
+    if (C > kMaxCorners) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: too many corners");
+    if (C > 0 && (!pos || !nrm || !uv || !idx)) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: null input stream");
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    HostCtx& c = g_ctx;
+    Trace tr;
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    if ((rc = c.pos.ensure(3 * np + 4))) return rc;
+    if ((rc = c.nrm.ensure(3 * nn + 4))) return rc;
+    if ((rc = c.uv.ensure(2 * nt + 4))) return rc;
+    if ((rc = c.idx.ensure(3 * C + 16))) return rc;
+    if (np) CU(cudaMemcpyAsync(c.pos.p, pos, np * 12, cudaMemcpyHostToDevice, c.st));
+    if (nn) CU(cudaMemcpyAsync(c.nrm.p, nrm, nn * 12, cudaMemcpyHostToDevice, c.st));
+    if (nt) CU(cudaMemcpyAsync(c.uv.p, uv, nt * 8, cudaMemcpyHostToDevice, c.st));
+    if (C) CU(cudaMemcpyAsync(c.idx.p, idx, C * 12, cudaMemcpyHostToDevice, c.st));
+    tr.mark("enqueue H2D");
+    return import_resident(c, c.pos.p, np, c.nrm.p, nn, c.uv.p, nt, c.idx.p, shape_off, nshapes, out, tr);
+}
+
+// For the library's OBJ-text entry point: the same import, with streams that already live on the device
+// (device pointers on g_ctx's device; the default stream must have finished writing them).
+int vkm_internal_import_device(int device, const float* d_pos, uint64_t np, const float* d_nrm, uint64_t nn,
+                               const float* d_uv, uint64_t nt, const int32_t* d_idx, const uint64_t* shape_off,
+                               uint32_t nshapes, vkm_shape_out* out) {
+    if (nshapes == 0) return VKM_OK;
+    init_shape_outs(out, nshapes);
+    std::lock_guard<std::mutex> lk(g_ctx.mu);
+    HostCtx& c = g_ctx;
+    if (c.devices[0] != device) c.devices[0] = device;
+    Trace tr;
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    return import_resident(c, d_pos, np, d_nrm, nn, d_uv, nt, d_idx, shape_off, nshapes, out, tr);
 }
 
 void* vkm_host_alloc(uint64_t bytes) {
