@@ -141,6 +141,16 @@ int vkm_e3dm_read(const char* path, char* mesh_name, int mesh_name_cap, vkm_e3dm
                   uint64_t* out_count);
 void vkm_e3dm_free(vkm_e3dm_config* configs, uint64_t count);
 
+/* ---- procedural generators.  Replace GeometryConfig GeometrySystem::GeneratePlainConfig(f32 width, f32 height,
+ *      u32 x_segment_count, u32 y_segment_count, f32 tile_x, f32 tile_y, name, material_name) and
+ *      GeometrySystem::GenerateCubeConfig(f32 width, f32 height, f32 depth, f32 tile_x, f32 tile_y, name,
+ *      material_name) -- engine/src/systems/geometry/geometry_system.cpp:182-294 and :296-439 (buffers only; the
+ *      names stay with the caller).  `deduplicate` runs Geometry::DeduplicateVertices on the plane, the follow-up
+ *      the reference's TODO at :227 names.  Buffers are malloc()ed; release with vkm_free_shape(). ---- */
+int vkm_generate_plane_config(float width, float height, uint32_t x_segment_count, uint32_t y_segment_count,
+                              float tile_x, float tile_y, int deduplicate, vkm_shape_out* out);
+int vkm_generate_cube_config(float width, float height, float depth, float tile_x, float tile_y, vkm_shape_out* out);
+
 /* Pinned host memory for callers that want full-speed PCIe transfers through the host entry points. */
 void* vkm_host_alloc(uint64_t bytes);
 void vkm_host_free(void* p);

@@ -163,6 +163,68 @@ uint32_t orc_deduplicate_vertices(uint32_t vertex_count, const orc_vertex* verti
 void orc_free(void* p) { free(p); }
 
 /* ------------------------------------------------------------------------------------------
+ * Procedural generators
+ * ---------------------------------------------------------------------------------------- */
+void orc_generate_plane(float width, float height, uint32_t xs, uint32_t ys, float tile_x, float tile_y,
+                        orc_vertex* v, uint32_t* indices) {
+    if (width == 0) width = 1.0f;
+    if (height == 0) height = 1.0f;
+    if (xs < 1) xs = 1;
+    if (ys < 1) ys = 1;
+    if (tile_x == 0) tile_x = 1.0f;
+    if (tile_y == 0) tile_y = 1.0f;
+    memset(v, 0, sizeof(orc_vertex) * 4u * xs * ys);
+    const float seg_w = width / xs, seg_h = height / ys, half_w = width * 0.5f, half_h = height * 0.5f;
+    for (uint32_t y = 0; y < ys; ++y)
+        for (uint32_t x = 0; x < xs; ++x) {
+            const float min_x = (x * seg_w) - half_w, min_y = (y * seg_h) - half_h;
+            const float max_x = min_x + seg_w, max_y = min_y + seg_h;
+            const float min_u = (x / (float)xs) * tile_x, min_v = (y / (float)ys) * tile_y;
+            const float max_u = ((x + 1) / (float)xs) * tile_x, max_v = ((y + 1) / (float)ys) * tile_y;
+            const uint32_t o = (y * xs + x) * 4;
+            const float px[4] = {min_x, max_x, min_x, max_x}, py[4] = {min_y, max_y, max_y, min_y};
+            const float pu[4] = {min_u, max_u, min_u, max_u}, pv[4] = {min_v, max_v, max_v, min_v};
+            for (int k = 0; k < 4; ++k) {
+                v[o + k].position[0] = px[k];
+                v[o + k].position[1] = py[k];
+                v[o + k].texcoord[0] = pu[k];
+                v[o + k].texcoord[1] = pv[k];
+            }
+            uint32_t* t = indices + (y * xs + x) * 6;
+            t[0] = o; t[1] = o + 1; t[2] = o + 2; t[3] = o; t[4] = o + 3; t[5] = o + 1;
+        }
+}
+
+void orc_generate_cube(float width, float height, float depth, float tile_x, float tile_y, orc_vertex* v,
+                       uint32_t* indices) {
+    if (width == 0) width = 1.0f;
+    if (height == 0) height = 1.0f;
+    if (depth == 0) depth = 1.0f;
+    if (tile_x == 0) tile_x = 1.0f;
+    if (tile_y == 0) tile_y = 1.0f;
+    const float hw = width * 0.5f, hh = height * 0.5f, hd = depth * 0.5f;
+    const float a = -hw, b = -hh, c = -hd, A = hw, B = hh, C = hd;
+    const float P[6][4][3] = {
+        {{a, b, C}, {A, B, C}, {a, B, C}, {A, b, C}}, {{A, b, c}, {a, B, c}, {A, B, c}, {a, b, c}},
+        {{a, b, c}, {a, B, C}, {a, B, c}, {a, b, C}}, {{A, b, C}, {A, B, c}, {A, B, C}, {A, b, c}},
+        {{A, b, C}, {a, b, c}, {A, b, c}, {a, b, C}}, {{a, B, C}, {A, B, c}, {a, B, c}, {A, B, C}},
+    };
+    const float UV[4][2] = {{0.f, 0.f}, {tile_x, tile_y}, {0.f, tile_y}, {tile_x, 0.f}};
+    memset(v, 0, sizeof(orc_vertex) * 24);
+    for (int f = 0; f < 6; ++f) {
+        for (int k = 0; k < 4; ++k) {
+            memcpy(v[4 * f + k].position, P[f][k], 12);
+            memcpy(v[4 * f + k].texcoord, UV[k], 8);
+        }
+        const uint32_t o = 4 * f;
+        uint32_t* t = indices + 6 * f;
+        t[0] = o; t[1] = o + 1; t[2] = o + 2; t[3] = o; t[4] = o + 3; t[5] = o + 1;
+    }
+    orc_generate_normals(24, v, 36, indices);
+    orc_generate_tangents(24, v, 36, indices);
+}
+
+/* ------------------------------------------------------------------------------------------
  * Import: expand + AABB + first-occurrence dedup + tangents, per shape
  * ---------------------------------------------------------------------------------------- */
 typedef struct {

@@ -57,6 +57,13 @@ uint32_t orc_deduplicate_vertices(uint32_t vertex_count, const orc_vertex* verti
                                   uint32_t* indices, orc_vertex** out_vertices);
 void orc_free(void* p);
 
+/* GeometrySystem::GeneratePlainConfig / GenerateCubeConfig, geometry_system.cpp:182-294 / :296-439 (buffers only).
+ * vertices: 4*xs*ys (plane) or 24 (cube) orc_vertex; indices: 6*xs*ys or 36 u32; caller allocates. */
+void orc_generate_plane(float width, float height, uint32_t xs, uint32_t ys, float tile_x, float tile_y,
+                        orc_vertex* vertices, uint32_t* indices);
+void orc_generate_cube(float width, float height, float depth, float tile_x, float tile_y, orc_vertex* vertices,
+                       uint32_t* indices);
+
 #ifdef __cplusplus
 }
 #endif

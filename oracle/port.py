@@ -51,6 +51,10 @@ def lib():
         L.orc_deduplicate_vertices.restype = C.c_uint32
         L.orc_deduplicate_vertices.argtypes = [C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_void_p)]
         L.orc_free.argtypes = [C.c_void_p]
+        L.orc_generate_plane.restype = None
+        L.orc_generate_plane.argtypes = [C.c_float, C.c_float, C.c_uint32, C.c_uint32, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_generate_cube.restype = None
+        L.orc_generate_cube.argtypes = [C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -106,3 +110,18 @@ def hash_vertex(v: np.ndarray) -> int:
 
 def vertex_equal(a: np.ndarray, b: np.ndarray) -> bool:
     return bool(lib().orc_vertex_equal(a.ctypes.data, b.ctypes.data))
+
+
+def generate_plane(width, height, xs, ys, tile_x, tile_y):
+    xs, ys = max(xs, 1), max(ys, 1)
+    v = np.zeros(4 * xs * ys, VERTEX_DTYPE)
+    i = np.zeros(6 * xs * ys, np.uint32)
+    lib().orc_generate_plane(width, height, xs, ys, tile_x, tile_y, v.ctypes.data, i.ctypes.data)
+    return v, i
+
+
+def generate_cube(width, height, depth, tile_x, tile_y):
+    v = np.zeros(24, VERTEX_DTYPE)
+    i = np.zeros(36, np.uint32)
+    lib().orc_generate_cube(width, height, depth, tile_x, tile_y, v.ctypes.data, i.ctypes.data)
+    return v, i

@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "resources/geometry/geometry.hpp"
+#include "systems/geometry/geometry_system.hpp"
 #include "systems/resource/loaders/mesh/mesh_loader.hpp"
 #include "systems/resource/resources/mesh/mesh_resource.hpp"
 #include "vendor/tinyobj/tinyobj.hpp"
@@ -186,6 +187,30 @@ uint32_t ref_deduplicate_vertices(uint32_t vc, void* v, uint32_t ic, uint32_t* i
     return n;
 }
 void ref_free(void* p) { std::free(p); }
+
+// ---------------- procedural generators (geometry_system.cpp:182-439) ----------------
+// GeneratePlainConfig / GenerateCubeConfig are non-static members that never touch the object; constructing a real
+// GeometrySystem would call into the renderer, so they are invoked on raw, suitably aligned storage.
+static Engine::GeometrySystem* fake_geometry_system() {
+    alignas(Engine::GeometrySystem) static unsigned char storage[sizeof(Engine::GeometrySystem)];
+    return reinterpret_cast<Engine::GeometrySystem*>(storage);
+}
+static void hand_over(Engine::GeometryConfig& c, uint32_t* vc, uint32_t* ic, void** v, void** idx) {
+    *vc = c.vertex_count;
+    *ic = c.index_count;
+    *v = c.vertices;   // malloc()ed by Platform::AllocMemory; release with ref_free
+    *idx = c.indices;
+}
+void ref_generate_plane(float width, float height, uint32_t xs, uint32_t ys, float tile_x, float tile_y, uint32_t* vc,
+                        uint32_t* ic, void** v, void** idx) {
+    Engine::GeometryConfig c = fake_geometry_system()->GeneratePlainConfig(width, height, xs, ys, tile_x, tile_y, "p", "m");
+    hand_over(c, vc, ic, v, idx);
+}
+void ref_generate_cube(float width, float height, float depth, float tile_x, float tile_y, uint32_t* vc, uint32_t* ic,
+                       void** v, void** idx) {
+    Engine::GeometryConfig c = fake_geometry_system()->GenerateCubeConfig(width, height, depth, tile_x, tile_y, "c", "m");
+    hand_over(c, vc, ic, v, idx);
+}
 
 // ---------------- std::hash<Vertex3D> / operator== (renderer_types.hpp:20-27,72-86) ----------------
 uint64_t ref_hash_vertex(const void* v64) { return std::hash<Engine::Vertex3D>()(*(const Engine::Vertex3D*)v64); }

@@ -68,6 +68,12 @@ def lib():
         L.ref_vertex_equal.restype = C.c_int
         L.ref_vertex_equal.argtypes = [C.c_void_p, C.c_void_p]
         L.ref_sizeof_vertex.restype = C.c_uint32
+        L.ref_generate_plane.restype = None
+        L.ref_generate_plane.argtypes = [C.c_float, C.c_float, C.c_uint32, C.c_uint32, C.c_float, C.c_float,
+                                         C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.ref_generate_cube.restype = None
+        L.ref_generate_cube.argtypes = [C.c_float, C.c_float, C.c_float, C.c_float, C.c_float,
+                                        C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
         _lib = L
     return _lib
 
@@ -226,3 +232,25 @@ def hash_vertex(v: np.ndarray) -> int:
 
 def vertex_equal(a: np.ndarray, b: np.ndarray) -> bool:
     return bool(lib().ref_vertex_equal(a.ctypes.data, b.ctypes.data))
+
+
+def _take(vc, ic, vp, ip):
+    v = np.frombuffer((C.c_char * (64 * vc.value)).from_address(vp.value), dtype=VERTEX_DTYPE).copy()
+    ix = np.frombuffer((C.c_char * (4 * ic.value)).from_address(ip.value), dtype=np.uint32).copy()
+    lib().ref_free(vp)
+    lib().ref_free(ip)
+    return v, ix
+
+
+def generate_plane(width, height, xs, ys, tile_x, tile_y):
+    """GeometrySystem::GeneratePlainConfig (geometry_system.cpp:182-294) -> (vertices, indices)."""
+    vc, ic, vp, ip = C.c_uint32(), C.c_uint32(), C.c_void_p(), C.c_void_p()
+    lib().ref_generate_plane(width, height, xs, ys, tile_x, tile_y, C.byref(vc), C.byref(ic), C.byref(vp), C.byref(ip))
+    return _take(vc, ic, vp, ip)
+
+
+def generate_cube(width, height, depth, tile_x, tile_y):
+    """GeometrySystem::GenerateCubeConfig (geometry_system.cpp:296-439) -> (vertices, indices)."""
+    vc, ic, vp, ip = C.c_uint32(), C.c_uint32(), C.c_void_p(), C.c_void_p()
+    lib().ref_generate_cube(width, height, depth, tile_x, tile_y, C.byref(vc), C.byref(ic), C.byref(vp), C.byref(ip))
+    return _take(vc, ic, vp, ip)

@@ -234,6 +234,25 @@ def test_deduplicate_vertices_edge_cases():
     assert len(gv) == len(wv) == 1 and np.array_equal(gi, wi)
 
 
+@pytest.mark.parametrize("case", [(10.0, 5.0, 3, 2, 2.0, 1.0), (1.0, 1.0, 1, 1, 1.0, 1.0), (7.3, 0.9, 170, 53, 3.0, 0.5),
+                                  (0.0, 0.0, 0, 0, 0.0, 0.0)])
+def test_procedural_generators_match_oracle(case):
+    w, h, xs, ys, tx, ty = case
+    gv, gi = capi.generate_plane_config(w, h, xs, ys, tx, ty)
+    pv, pi = port.generate_plane(w, h, xs, ys, tx, ty)
+    assert gv.tobytes() == pv.tobytes() and np.array_equal(gi, pi)
+    gv, gi = capi.generate_cube_config(w, h, 2.5 * w, tx, ty)
+    pv, pi = port.generate_cube(w, h, 2.5 * w, tx, ty)
+    ok, msg = vertices_equal(gv, pv)
+    assert ok and np.array_equal(gi, pi), msg
+    # the plane followed by DeduplicateVertices (the reference's TODO at geometry_system.cpp:227)
+    if xs * ys <= 64:
+        dv, di = capi.generate_plane_config(w, h, xs, ys, tx, ty, deduplicate=True)
+        wv, wi = port.deduplicate_vertices(pv if False else port.generate_plane(w, h, xs, ys, tx, ty)[0],
+                                           port.generate_plane(w, h, xs, ys, tx, ty)[1])
+        assert dv.tobytes() == wv.tobytes() and np.array_equal(di, wi)
+
+
 # ---------------------------------------------------------------- device-resident plan API
 def test_plan_device_resident_matches_host_entry():
     m = synth.concat([synth.grid(64), synth.uv_sphere(12, 24), synth.adversarial(32)])

@@ -180,3 +180,26 @@ def test_reference_obj_text_path_equals_injected_arrays(tmp_path):
     a = refcpu.load_obj(str(p), "sphere")
     b = refcpu.import_arrays(m.pos, m.nrm, m.uv, m.idx, m.shape_offsets)
     assert_shapes_equal(a, b)
+
+
+GEN_CASES = [(10.0, 5.0, 3, 2, 2.0, 1.0), (1.0, 1.0, 1, 1, 1.0, 1.0), (7.3, 0.9, 17, 5, 3.0, 0.5), (0.0, 0.0, 0, 0, 0.0, 0.0)]
+
+
+@needs_ref
+@pytest.mark.parametrize("case", GEN_CASES)
+def test_port_generators_match_reference_code(case):
+    w, h, xs, ys, tx, ty = case
+    rv, ri = refcpu.generate_plane(w, h, xs, ys, tx, ty)
+    pv, pi = port.generate_plane(w, h, xs, ys, tx, ty)
+    assert rv.tobytes() == pv.tobytes() and np.array_equal(ri, pi)
+    rv, ri = refcpu.generate_cube(w, h, 2.5 * w, tx, ty)
+    pv, pi = port.generate_cube(w, h, 2.5 * w, tx, ty)
+    ok, msg = vertices_equal(rv, pv)
+    assert ok and np.array_equal(ri, pi), msg
+
+
+def test_port_cube_is_the_golden_cube():
+    g = load_golden("cube")
+    v, i = port.generate_cube(2.0, 2.0, 2.0, 1.0, 1.0)
+    ok, msg = vertices_equal(v, g["vertices_out"])
+    assert ok and np.array_equal(i, g["indices"]), msg

@@ -28,7 +28,7 @@ SYMBOLS = [
     "vkm_generate_tangents", "vkm_generate_normals", "vkm_deduplicate_vertices",
     "vkm_import_shapes", "vkm_free_shape", "vkm_host_alloc", "vkm_host_free",
     "vkm_e3dm_write", "vkm_e3dm_read", "vkm_e3dm_free", "vkm_parse_obj", "vkm_free_obj_streams",
-    "vkm_import_obj_text", "vkm_free_obj_import",
+    "vkm_import_obj_text", "vkm_free_obj_import", "vkm_generate_plane_config", "vkm_generate_cube_config",
     "vkm_plan_create", "vkm_plan_destroy", "vkm_plan_import", "vkm_plan_finish", "vkm_plan_set_timing",
     "vkm_plan_phase_name", "vkm_generate_tangents_dev", "vkm_generate_normals_dev",
     "vkm_generate_tangents_dev_noalloc",
@@ -127,6 +127,10 @@ def lib():
     L.vkm_import_obj_text.restype = C.c_int
     L.vkm_import_obj_text.argtypes = [C.c_int, C.c_char_p, C.c_uint64, C.POINTER(ObjImport)]
     L.vkm_free_obj_import.argtypes = [C.POINTER(ObjImport)]
+    L.vkm_generate_plane_config.restype = C.c_int
+    L.vkm_generate_plane_config.argtypes = [C.c_float, C.c_float, C.c_uint32, C.c_uint32, C.c_float, C.c_float, C.c_int, C.POINTER(ShapeOut)]
+    L.vkm_generate_cube_config.restype = C.c_int
+    L.vkm_generate_cube_config.argtypes = [C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.POINTER(ShapeOut)]
     L.vkm_host_alloc.restype = C.c_void_p
     L.vkm_host_alloc.argtypes = [C.c_uint64]
     L.vkm_host_free.argtypes = [C.c_void_p]
@@ -301,6 +305,25 @@ def import_obj_text(text: bytes, device: int = 0):
         return shapes, names, mats
     finally:
         L.vkm_free_obj_import(C.byref(r))
+
+
+def _take_shape(o):
+    v = _copy_out(o.vertices, 64 * o.vertex_count, VERTEX_DTYPE)
+    ix = _copy_out(o.indices, 4 * o.index_count, np.uint32)
+    lib().vkm_free_shape(C.byref(o))
+    return v, ix
+
+
+def generate_plane_config(width, height, xs, ys, tile_x, tile_y, deduplicate=False):
+    o = ShapeOut()
+    _check(lib().vkm_generate_plane_config(width, height, xs, ys, tile_x, tile_y, 1 if deduplicate else 0, C.byref(o)))
+    return _take_shape(o)
+
+
+def generate_cube_config(width, height, depth, tile_x, tile_y):
+    o = ShapeOut()
+    _check(lib().vkm_generate_cube_config(width, height, depth, tile_x, tile_y, C.byref(o)))
+    return _take_shape(o)
 
 
 def e3dm_write(path: str, mesh_name: str, shapes: list, names: list, material_names: list) -> None:
