@@ -24,7 +24,9 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
@@ -38,6 +40,17 @@ extern "C" int vkm_internal_import_device(int device, const float* d_pos, uint64
 namespace {
 
 void perr(const std::string& m) { vkm_internal_set_error(m.c_str()); }
+
+struct PTrace {  // VKM_TRACE=1: host-side time line on stderr
+    bool on = getenv("VKM_TRACE") != nullptr;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    void mark(const char* what) {
+        if (!on) return;
+        const auto t = std::chrono::steady_clock::now();
+        fprintf(stderr, "[vkm parse] %-26s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t - t0).count());
+        t0 = t;
+    }
+};
 
 constexpr int kT = 256;
 enum Kind : uint8_t { K_SKIP = 0, K_V, K_VN, K_VT, K_F, K_O, K_G, K_USEMTL, K_BAD };
@@ -510,6 +523,7 @@ static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_stream
         return VKM_ERR_NO_DEVICE;
     }
     int rc = VKM_OK;
+    PTrace ptr;
     // pow tables from the host libm: the same doubles tinyobj's std::pow calls produce on this machine
     constexpr int kP10 = 400, kBias = 1100;
     std::vector<double> h_p10(kP10), h_p5(2 * kBias + 1);
@@ -534,6 +548,7 @@ static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_stream
     const uint32_t nt1 = std::max<uint32_t>(1, (nwords + kSTile - 1) / kSTile);
     cudaStream_t st = nullptr;
 
+    ptr.mark("pow tables");
     PCU(cudaSetDevice(device));
     PCU(cudaMalloc(&d_text, len + 1));
     PCU(cudaMalloc(&d_bits, (uint64_t)(nwords + 1) * 4));
@@ -555,6 +570,7 @@ static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_stream
         PCU(cudaMemcpyAsync(&nlines, d_tot, 4, cudaMemcpyDeviceToHost, st));
         PCU(cudaStreamSynchronize(st));
     }
+    ptr.mark("alloc + H2D + line scan");
     if (nlines) {
         const uint64_t L = nlines;
         const uint32_t nt2 = std::max<uint32_t>(1, (nlines + kSTile - 1) / kSTile);
@@ -572,6 +588,7 @@ static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_stream
         PCU(cudaMemcpyAsync(tot, d_tot, 20, cudaMemcpyDeviceToHost, st));
         PCU(cudaMemcpyAsync(&hst, d_st, sizeof hst, cudaMemcpyDeviceToHost, st));
         PCU(cudaStreamSynchronize(st));
+        ptr.mark("classify + count scans");
         if (hst.unsupported) {
             perr("line " + std::to_string(hst.first_bad_line + 1) + ": construct left to the CPU parser (polygon with more than 4 corners, l / p / vw / t record)");
             rc = VKM_ERR_UNSUPPORTED;
@@ -590,6 +607,7 @@ static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_stream
         special.resize(tot[4]);
         if (tot[4]) PCU(cudaMemcpyAsync(special.data(), d_sp, (uint64_t)tot[4] * 8, cudaMemcpyDeviceToHost, st));
         PCU(cudaStreamSynchronize(st));
+        ptr.mark("parse records + faces");
         if (hst.bad_face) {
             perr("line " + std::to_string(hst.first_bad_line + 1) + ": face with a zero or unresolvable vertex index (tinyobj fails the load here)");
             rc = VKM_ERR_BAD_INDEX;
@@ -610,6 +628,7 @@ static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_stream
             if (tot[3]) PCU(cudaMemcpyAsync(out->idx_vnt, d_idx, (uint64_t)tot[3] * 36, cudaMemcpyDeviceToHost, st));
         }
         PCU(cudaStreamSynchronize(st));
+        ptr.mark("D2H streams");
         // ---- shapes (host; the o / g / usemtl lines are few): a shape = the faces between two o/g lines
         auto line_text = [&](uint32_t line_start_byte) {
             const char* b = text + line_start_byte;
@@ -688,9 +707,11 @@ static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_stream
         }
     }
 done:
+    ptr.mark("shapes / import");
     cudaFree(d_text); cudaFree(d_bits); cudaFree(d_bpre); cudaFree(d_sums); cudaFree(d_tot); cudaFree(d_ls);
     cudaFree(d_cnt); cudaFree(d_off); cudaFree(d_kind); cudaFree(d_p10); cudaFree(d_p5); cudaFree(d_pos);
     cudaFree(d_nrm); cudaFree(d_uv); cudaFree(d_idx); cudaFree(d_sp); cudaFree(d_st);
+    ptr.mark("cudaFree");
     if (rc != VKM_OK) vkm_free_obj_streams(out);
     return rc;
 }
