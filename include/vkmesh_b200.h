@@ -95,6 +95,22 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
                       vkm_shape_out* out);
 void vkm_free_shape(vkm_shape_out* shape);
 
+/* A batch of independent meshes (each what one vkm_import_shapes call takes) over every GPU selected with
+ * vkm_init(): the multi-GPU form of the same reference loop (each mesh is an independent dedup domain,
+ * mesh_loader.cpp:322-324 clears all state between shapes; the reference itself has no multi-mesh entry).  Meshes
+ * are partitioned over the devices by size (longest first); each device runs two lanes so that one mesh's copies
+ * overlap another's kernels.  outs[i] must hold meshes[i].nshapes entries; statuses (optional) gets one code per
+ * mesh.  Returns the first failure's code, VKM_OK if every mesh imported. */
+typedef struct vkm_mesh_in {
+    const float* pos;  uint64_t np;
+    const float* nrm;  uint64_t nn;
+    const float* uv;   uint64_t nt;
+    const int32_t* idx_vnt;
+    const uint64_t* shape_corner_offsets; /* nshapes + 1 */
+    uint32_t nshapes;
+} vkm_mesh_in;
+int vkm_import_batch(const vkm_mesh_in* meshes, uint32_t count, vkm_shape_out* const* outs, int* statuses);
+
 /* ---- OBJ text -> tinyobj-shaped streams on the GPU.  Replaces, for `v`/`vn`/`vt` records, triangle and quad
  *      faces, `o`/`g` shapes and `usemtl`, the call tinyobj::LoadObj(&attributes, &shapes, &materials, ...) in
  *      MeshLoader::LoadOBJ (mesh_loader.cpp:219; parser tinyobj.hpp:2557-3115) -- same floats (the parser's own

@@ -320,6 +320,23 @@ def test_headless_renderer_handoff_pool():
     plan.destroy()
 
 
+def test_import_batch_pipelined_lanes_match_oracle():
+    """vkm_import_batch: independent meshes over the selected GPUs, two overlapping lanes per GPU."""
+    meshes = [synth.grid(40), synth.uv_sphere(12, 30), synth.adversarial(30), synth.grid(3),
+              synth.concat([synth.grid(8), synth.grid(5)]), synth.grid(90, permute_seed=4), synth.adversarial(60)]
+    got = capi.import_batch(meshes)
+    assert len(got) == len(meshes)
+    for g, m in zip(got, meshes):
+        assert_shapes_equal(g, oracle_of(m))
+    # a failing mesh is reported by position and does not poison the others
+    bad = synth.grid(4)
+    bad.idx = bad.idx.copy()
+    bad.idx[2, 1] = -1
+    with pytest.raises(capi.VkmError) as e:
+        capi.import_batch([synth.grid(5), bad])
+    assert e.value.code == 2 and "mesh 1" in str(e.value)
+
+
 # ---------------------------------------------------------------- full-size property checks (no oracle run)
 def test_config3_16m_properties():
     """16.7M-triangle high-duplication grid: too slow for the CPU oracle inside the test budget, so check

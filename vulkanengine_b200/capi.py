@@ -26,7 +26,7 @@ ERR_NAMES = {1: "INVALID_ARG", 2: "BAD_INDEX", 3: "OOM", 4: "CUDA", 5: "NO_DEVIC
 SYMBOLS = [
     "vkm_device_count", "vkm_init", "vkm_shutdown", "vkm_last_error", "vkm_version",
     "vkm_generate_tangents", "vkm_generate_normals", "vkm_deduplicate_vertices",
-    "vkm_import_shapes", "vkm_free_shape", "vkm_host_alloc", "vkm_host_free",
+    "vkm_import_shapes", "vkm_free_shape", "vkm_host_alloc", "vkm_host_free", "vkm_import_batch",
     "vkm_e3dm_write", "vkm_e3dm_read", "vkm_e3dm_free", "vkm_parse_obj", "vkm_free_obj_streams",
     "vkm_import_obj_text", "vkm_free_obj_import", "vkm_generate_plane_config", "vkm_generate_cube_config",
     "vkm_plan_create", "vkm_plan_destroy", "vkm_plan_import", "vkm_plan_finish", "vkm_plan_set_timing",
@@ -53,6 +53,11 @@ class ShapeOut(C.Structure):
     _fields_ = [("vertex_size", C.c_uint32), ("vertex_count", C.c_uint32), ("vertices", C.c_void_p),
                 ("index_size", C.c_uint32), ("index_count", C.c_uint32), ("indices", C.c_void_p),
                 ("extent", Extent)]
+
+
+class MeshIn(C.Structure):
+    _fields_ = [("pos", C.c_void_p), ("np", C.c_uint64), ("nrm", C.c_void_p), ("nn", C.c_uint64), ("uv", C.c_void_p),
+                ("nt", C.c_uint64), ("idx_vnt", C.c_void_p), ("shape_corner_offsets", C.c_void_p), ("nshapes", C.c_uint32)]
 
 
 class E3dmConfig(C.Structure):
@@ -116,6 +121,8 @@ def lib():
     L.vkm_import_shapes.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p,
                                     C.c_void_p, C.c_uint32, C.POINTER(ShapeOut)]
     L.vkm_free_shape.argtypes = [C.POINTER(ShapeOut)]
+    L.vkm_import_batch.restype = C.c_int
+    L.vkm_import_batch.argtypes = [C.POINTER(MeshIn), C.c_uint32, C.POINTER(C.POINTER(ShapeOut)), C.POINTER(C.c_int)]
     L.vkm_e3dm_write.restype = C.c_int
     L.vkm_e3dm_write.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(E3dmConfig), C.c_uint64]
     L.vkm_e3dm_read.restype = C.c_int
@@ -227,6 +234,41 @@ def import_shapes(pos, nrm, uv, idx, shape_offsets) -> list:
         e = np.array(list(o.extent.center) + list(o.extent.min_extents) + list(o.extent.max_extents), np.float32)
         res.append(ShapeResult(v, ix, e))
         L.vkm_free_shape(C.byref(o))
+    return res
+
+
+def import_batch(meshes: list) -> list:
+    """vkm_import_batch: a list of objects with pos/nrm/uv/idx/shape_offsets -> list of lists of ShapeResult."""
+    L = lib()
+    n = len(meshes)
+    ins = (MeshIn * max(n, 1))()
+    outs = (C.POINTER(ShapeOut) * max(n, 1))()
+    keep, arrays = [], []
+    for i, m in enumerate(meshes):
+        pos = np.ascontiguousarray(m.pos, np.float32)
+        nrm = np.ascontiguousarray(m.nrm, np.float32)
+        uv = np.ascontiguousarray(m.uv, np.float32)
+        idx = np.ascontiguousarray(m.idx, np.int32)
+        so = np.ascontiguousarray(m.shape_offsets, np.uint64)
+        keep += [pos, nrm, uv, idx, so]
+        ns = len(so) - 1
+        ins[i] = MeshIn(pos.ctypes.data, pos.size // 3, nrm.ctypes.data, nrm.size // 3, uv.ctypes.data, uv.size // 2,
+                        idx.ctypes.data, so.ctypes.data, ns)
+        arr = (ShapeOut * max(ns, 1))()
+        arrays.append((arr, ns))
+        outs[i] = C.cast(arr, C.POINTER(ShapeOut))
+    st = (C.c_int * max(n, 1))()
+    _check(L.vkm_import_batch(ins, n, outs, st))
+    res = []
+    for arr, ns in arrays:
+        shapes = []
+        for k in range(ns):
+            o = arr[k]
+            e = np.array(list(o.extent.center) + list(o.extent.min_extents) + list(o.extent.max_extents), np.float32)
+            shapes.append(ShapeResult(_copy_out(o.vertices, 64 * o.vertex_count, VERTEX_DTYPE),
+                                      _copy_out(o.indices, 4 * o.index_count, np.uint32), e))
+            L.vkm_free_shape(C.byref(o))
+        res.append(shapes)
     return res
 
 

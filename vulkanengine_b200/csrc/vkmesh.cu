@@ -8,6 +8,7 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdarg>
 #include <cstdio>
@@ -599,8 +600,11 @@ struct HostCtx {
     char* h_stage = nullptr;
     uint64_t h_stage_cap = 0;
     std::vector<cudaEvent_t> chunk_ev;
+    unsigned copy_threads = 8;  // host threads that move finished chunks into the result buffers
 };
-HostCtx g_ctx;
+HostCtx g_ctx;                  // the lane behind the single-call host entry points
+std::mutex g_lanes_mu;
+std::vector<HostCtx*> g_lanes;  // vkm_import_batch: 2 per device, created on first use, released by vkm_shutdown
 
 // Device-to-host leg of the host entry point.  The engine wants malloc()ed buffers; a direct copy into fresh
 // pageable memory runs at a few GB/s (driver bounce buffers + first-touch page faults on one thread).  Instead
@@ -656,7 +660,7 @@ int download_staged(HostCtx& c, const void* d_vertices, uint64_t vbytes, const v
         CU(cudaEventRecord(c.chunk_ev[k], c.st));
     }
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-    const unsigned nthreads = (unsigned)std::min<uint64_t>(std::min(8u, hw), nchunks);
+    const unsigned nthreads = (unsigned)std::min<uint64_t>(std::min(std::max(1u, c.copy_threads), hw), nchunks);
     const int dev = c.bound_device;
     std::vector<int> errs(nthreads, 0);
     auto work = [&](unsigned t) {
@@ -686,6 +690,8 @@ int ctx_bind(HostCtx& c) {
         if (c.plan) { vkm_plan_destroy(c.plan); c.plan = nullptr; }
         c.pos.release(); c.nrm.release(); c.uv.release(); c.idx.release(); c.vtx.release(); c.ind.release();
         c.scratch.release(); c.flag.release();
+        for (auto e : c.chunk_ev) cudaEventDestroy(e);  // events belong to the device they were created on
+        c.chunk_ev.clear();
         if (c.st) cudaStreamDestroy(c.st);
         c.st = nullptr;
         CU(cudaStreamCreateWithFlags(&c.st, cudaStreamNonBlocking));
@@ -734,9 +740,21 @@ int vkm_init(const int* device_ordinals, int count) {
     return ctx_bind(g_ctx);
 }
 
+static void release_ctx(HostCtx& c);
+
 void vkm_shutdown(void) {
+    {
+        std::lock_guard<std::mutex> lk(g_lanes_mu);
+        for (HostCtx* l : g_lanes) {
+            std::lock_guard<std::mutex> lk2(l->mu);
+            release_ctx(*l);
+        }
+    }
     std::lock_guard<std::mutex> lk(g_ctx.mu);
-    HostCtx& c = g_ctx;
+    release_ctx(g_ctx);
+}
+
+static void release_ctx(HostCtx& c) {
     if (c.bound_device < 0) return;
     cudaSetDevice(c.bound_device);
     if (c.plan) { vkm_plan_destroy(c.plan); c.plan = nullptr; }
@@ -885,16 +903,16 @@ static void init_shape_outs(vkm_shape_out* out, uint32_t nshapes) {
     }
 }
 
-int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t nn, const float* uv, uint64_t nt,
-                      const int32_t* idx, const uint64_t* shape_off, uint32_t nshapes, vkm_shape_out* out) {
+// vkm_import_shapes on one lane (a HostCtx: device, stream, plan, staging).  Takes the lane's lock.
+static int lane_import(HostCtx& c, const float* pos, uint64_t np, const float* nrm, uint64_t nn, const float* uv,
+                       uint64_t nt, const int32_t* idx, const uint64_t* shape_off, uint32_t nshapes, vkm_shape_out* out) {
     if (nshapes == 0) return VKM_OK;
     if (!shape_off || !out) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: null argument");
     init_shape_outs(out, nshapes);
     const uint64_t C = shape_off[nshapes];
     if (C > kMaxCorners) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: too many corners");
     if (C > 0 && (!pos || !nrm || !uv || !idx)) return fail(VKM_ERR_INVALID_ARG, "vkm_import_shapes: null input stream");
-    std::lock_guard<std::mutex> lk(g_ctx.mu);
-    HostCtx& c = g_ctx;
+    std::lock_guard<std::mutex> lk(c.mu);
     Trace tr;
     int rc = ctx_bind(c);
     if (rc) return rc;
@@ -908,6 +926,79 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
     if (C) CU(cudaMemcpyAsync(c.idx.p, idx, C * 12, cudaMemcpyHostToDevice, c.st));
     tr.mark("enqueue H2D");
     return import_resident(c, c.pos.p, np, c.nrm.p, nn, c.uv.p, nt, c.idx.p, shape_off, nshapes, out, tr);
+}
+
+int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t nn, const float* uv, uint64_t nt,
+                      const int32_t* idx, const uint64_t* shape_off, uint32_t nshapes, vkm_shape_out* out) {
+    return lane_import(g_ctx, pos, np, nrm, nn, uv, nt, idx, shape_off, nshapes, out);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Batches of independent meshes over every selected GPU: the natural shard.
+// Meshes are partitioned over the devices of vkm_init() by longest-processing-time (corner count); every device
+// runs TWO lanes (own stream, plan, device inputs, pinned staging, host thread), so the host->device copy of one
+// mesh overlaps the kernels and the device->host copy of another (the copy engines are full duplex).  No
+// inter-GPU traffic: results land in the caller's per-mesh output arrays.
+// ------------------------------------------------------------------------------------------------
+int vkm_import_batch(const vkm_mesh_in* meshes, uint32_t count, vkm_shape_out* const* outs, int* statuses) {
+    if (count == 0) return VKM_OK;
+    if (!meshes || !outs) return fail(VKM_ERR_INVALID_ARG, "vkm_import_batch: null argument");
+    if (vkm_device_count() == 0) return fail(VKM_ERR_NO_DEVICE, "no CUDA device: vkmesh_b200 has no CPU path");
+    std::vector<int> devices;
+    {
+        std::lock_guard<std::mutex> lk(g_ctx.mu);
+        devices = g_ctx.devices;
+    }
+    const size_t nd = devices.size();
+    std::lock_guard<std::mutex> batch_lock(g_lanes_mu);  // one batch at a time
+    while (g_lanes.size() < 2 * nd) g_lanes.push_back(new HostCtx());
+    for (size_t k = 0; k < 2 * nd; ++k) {
+        g_lanes[k]->devices[0] = devices[k / 2];
+        g_lanes[k]->copy_threads = 8;
+    }
+    // LPT partition by corner count (deterministic: ties by mesh id)
+    std::vector<uint32_t> order(count);
+    for (uint32_t i = 0; i < count; ++i) order[i] = i;
+    auto size_of = [&](uint32_t i) { return meshes[i].nshapes ? meshes[i].shape_corner_offsets[meshes[i].nshapes] : 0; };
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return size_of(a) > size_of(b); });
+    std::vector<std::vector<uint32_t>> queue(nd);
+    std::vector<uint64_t> load(nd, 0);
+    for (uint32_t i : order) {
+        size_t best = 0;
+        for (size_t d = 1; d < nd; ++d)
+            if (load[d] < load[best]) best = d;
+        queue[best].push_back(i);
+        load[best] += size_of(i);
+    }
+    std::vector<int> st(count, VKM_OK);
+    std::vector<std::string> msgs(count);
+    std::vector<std::atomic<uint32_t>> next(nd);
+    for (auto& n : next) n.store(0);
+    auto work = [&](size_t lane) {
+        const size_t d = lane / 2;
+        for (;;) {
+            const uint32_t k = next[d].fetch_add(1);
+            if (k >= queue[d].size()) return;
+            const uint32_t i = queue[d][k];
+            const vkm_mesh_in& m = meshes[i];
+            st[i] = lane_import(*g_lanes[lane], m.pos, m.np, m.nrm, m.nn, m.uv, m.nt, m.idx_vnt, m.shape_corner_offsets,
+                                m.nshapes, outs[i]);
+            if (st[i] != VKM_OK) msgs[i] = g_err;  // thread-local message of this worker
+        }
+    };
+    std::vector<std::thread> pool;
+    for (size_t lane = 1; lane < 2 * nd; ++lane) pool.emplace_back(work, lane);
+    work(0);
+    for (auto& t : pool) t.join();
+    int rc = VKM_OK;
+    for (uint32_t i = 0; i < count; ++i) {
+        if (statuses) statuses[i] = st[i];
+        if (st[i] != VKM_OK && rc == VKM_OK) {
+            rc = st[i];
+            g_err = "mesh " + std::to_string(i) + ": " + msgs[i];
+        }
+    }
+    return rc;
 }
 
 // For the library's OBJ-text entry point: the same import, with streams that already live on the device
