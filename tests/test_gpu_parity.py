@@ -337,6 +337,20 @@ def test_import_batch_pipelined_lanes_match_oracle():
     assert e.value.code == 2 and "mesh 1" in str(e.value)
 
 
+def test_import_batch_over_two_gpus_in_one_process():
+    """The native multi-GPU scheduler: needs two visible devices (skipped on a one-GPU box)."""
+    if capi.lib().vkm_device_count() < 2:
+        pytest.skip("one GPU visible")
+    meshes = [synth.grid(30 + 7 * i) for i in range(6)] + [synth.adversarial(25), synth.uv_sphere(10, 18)]
+    capi.init([0, 1])
+    try:
+        got = capi.import_batch(meshes)
+        for g, m in zip(got, meshes):
+            assert_shapes_equal(g, oracle_of(m))
+    finally:
+        capi.init([0])
+
+
 # ---------------------------------------------------------------- full-size property checks (no oracle run)
 def test_config3_16m_properties():
     """16.7M-triangle high-duplication grid: too slow for the CPU oracle inside the test budget, so check
