@@ -155,6 +155,27 @@ def test_many_triplets_per_attribute_record_falls_back_to_scrambled_table():
     assert_shapes_equal(gpu_of(g), oracle_of(g))
 
 
+def test_key_attribute_is_the_largest_array_whichever_it_is():
+    """Mode-0 addressing keys the triplet table on the largest attribute array: v (grids), vt (uv sphere), and here
+    vn (flat shading: one normal record per face) -- all three template instantiations of the insert kernel."""
+    g = synth.grid(24)
+    f = g.triangles
+    rng = np.random.default_rng(12)
+    nrm = rng.standard_normal((f, 3)).astype(np.float32)
+    idx = g.idx.copy()
+    idx[:, 1] = np.repeat(np.arange(f, dtype=np.int32), 3)
+    assert len(nrm) > len(g.pos) and len(nrm) > len(g.uv)
+    got = capi.import_shapes(g.pos, nrm, g.uv, idx, g.shape_offsets)
+    assert_shapes_equal(got, port.import_arrays(g.pos, nrm, g.uv, idx, g.shape_offsets))
+    # three variants of one key record (probe >= 2 -> displaced entries -> the exact fallback for triplet lookups)
+    pos = np.tile(g.pos[:1], (4, 1)).astype(np.float32) + np.arange(4, dtype=np.float32)[:, None]
+    uv = rng.random((40, 2)).astype(np.float32)
+    nr = rng.standard_normal((3, 3)).astype(np.float32)
+    idx2 = np.stack([rng.integers(0, 4, 300), rng.integers(0, 3, 300), np.arange(300) % 40], 1).astype(np.int32)
+    so = np.array([0, 300], np.uint64)
+    assert_shapes_equal(capi.import_shapes(pos, nr, uv, idx2, so), port.import_arrays(pos, nr, uv, idx2, so))
+
+
 def test_value_duplicates_with_distinct_triplets_merge():
     # every attribute record exists twice: 8 different triplets per vertex value
     g = synth.grid(20)

@@ -55,10 +55,6 @@ struct PTrace {  // VKM_TRACE=1: host-side time line on stderr
 constexpr int kT = 256;
 enum Kind : uint8_t { K_SKIP = 0, K_V, K_VN, K_VT, K_F, K_O, K_G, K_USEMTL, K_BAD };
 
-struct Counts {  // per line, then exclusive prefix
-    uint32_t v, vn, vt, tri, special;
-};
-
 struct ParseStatus {
     uint32_t unsupported;  // polygon > 4, l / p / vw / t lines
     uint32_t bad_face;     // zero / unresolvable vertex index
