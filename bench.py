@@ -311,20 +311,26 @@ def main():
     dom = int(np.argmax(phase_ms[: len(names)]))
     dom_name = names[dom]
     kernels = {nm: {"ms": float(phase_ms[i]), "algorithmic_bytes": int(share.get(nm, 0))} for i, nm in enumerate(names)}
-    traffic = None
+    tmap = {}
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get(args.workload, {}).get(dom_name)
+            tmap = {k: v for k, v in json.load(open(tpath)).get(args.workload, {}).items() if not k.startswith("_")}
         except Exception:
-            traffic = None
+            tmap = {}
     dom_bytes = share.get(dom_name, 0)
     dom_ach = dom_bytes / (phase_ms[dom] * 1e-3) / 1e9 if phase_ms[dom] > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": dom_name, "achieved": dom_ach, "peak": peak, "unit": "GB/s",
-                "frac": dom_ach / peak, "traffic": traffic, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": int(dom_bytes), "ms_per_launch": float(phase_ms[dom]),
-                "share_of_step": float(phase_ms[dom] / max(phase_ms.sum(), 1e-9))}
+    dominant = {"kernel": dom_name, "achieved": dom_ach, "peak": peak, "unit": "GB/s", "frac": dom_ach / peak,
+                "traffic": tmap.get(dom_name), "algorithmic_bytes_per_launch": int(dom_bytes),
+                "ms_per_launch": float(phase_ms[dom]), "share_of_step": float(phase_ms[dom] / max(phase_ms.sum(), 1e-9)),
+                "note": "algorithmic bytes this phase is the first to read / the one to write (the phases' shares sum to B_alg)"}
+    # roofline.achieved = B_alg / t_pipeline (the step is one import = 7 launches); the dominant
+    # launch is broken out beside it, and every phase with its time and owned bytes under pipeline_roofline.
     pipe_ach = b_alg / (ms_per_step * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": pipe_ach, "peak": peak, "unit": "GB/s", "frac": pipe_ach / peak,
+                "traffic": (sum(tmap.values()) if tmap else None), "peak_source": peak_src,
+                "scope": "whole step = one import (B_alg / t_step, SURVEY.md 8(d)); traffic = ncu DRAM bytes of its launches",
+                "algorithmic_bytes_per_step": int(b_alg), "dominant_kernel": dominant}
     pipeline_roofline = {"bound": "hbm", "achieved": pipe_ach, "peak": peak, "unit": "GB/s", "frac": pipe_ach / peak,
                          "algorithmic_bytes_per_step": int(b_alg), "bytes_per_triangle": b_alg / F, "kernels": kernels}
 

@@ -8,6 +8,6 @@ import json
 d = json.load(open("gpurun_out/bench_quick.json"))
 print("Gtris/s %.3f  ms/step %.4f  pipeline frac %.4f" % (d["value"] / 1e9, d["ms_per_step"], d["pipeline_roofline"]["frac"]))
 print({k: round(v["ms"], 4) for k, v in d["pipeline_roofline"]["kernels"].items()})
-print("roofline", {k: d["roofline"][k] for k in ("kernel", "achieved", "frac")})
+print("roofline", {k: d["roofline"][k] for k in ("achieved", "frac", "traffic")}, "dominant", {k: d["roofline"]["dominant_kernel"][k] for k in ("kernel", "frac", "share_of_step")})
 print("e2e", d["e2e"]["value"] / 1e6, "Mtris/s", d["e2e"]["ms_per_step"], "ms; single", d["e2e"].get("single_call"), d["clocks"])
 PY
