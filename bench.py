@@ -300,13 +300,14 @@ def main():
     b_alg = mesh.algorithmic_bytes(U)
     names = plan.phase_names()
     # algorithmic bytes each phase is the first to read / the one to write (they sum to B_alg)
+    # (timed imports run the short schedule: the value-level proof, and with it the first read of the attribute
+    # arrays, rides along in the vertex pass; `resolve_values` only sets the flag bits)
     share = {
         "insert_triplets": 36 * F,                                                  # the (v,n,t) index stream
-        "resolve_values": mesh.pos.nbytes + mesh.nrm.nbytes + mesh.uv.nbytes + 36,  # attribute arrays + extent
-        "indices": 12 * F,                                                     # u32 index buffer
-        "vertices": 48 * U,                                                    # Vertex3D minus tangent
-        "tangents": 16 * U,                                                    # tangent column
-        "clear": 0, "mark_scan": 0,
+        "resolve_values": 0,
+        "indices": 12 * F,                                                          # u32 index buffer
+        "vertices": 64 * U + mesh.pos.nbytes + mesh.nrm.nbytes + mesh.uv.nbytes + 36 * nshapes,  # Vertex3D + attributes + extents
+        "tangents": 0, "clear": 0, "mark_scan": 0,
     }
     dom = int(np.argmax(phase_ms[: len(names)]))
     dom_name = names[dom]

@@ -542,12 +542,35 @@ __device__ __forceinline__ void store_vertex(float4* dst, const uint32_t k[8], f
     __stcs(dst + 3, tangent);
 }
 
+// Short schedule only: flag the first corner of every distinct triplet (speculation: the import is clean).
+__global__ void __launch_bounds__(kThreads) k_flag_firsts(ImportArgs a) {
+    const uint32_t npairs = a.m1 >> 1;
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npairs; p += gridDim.x * blockDim.x) {
+        const uint2 cc = __ldcs(reinterpret_cast<const uint2*>(a.table1) + p);
+        if (cc.x != kEmpty32 && cc.x < a.ncorners) atomicOr(a.fbits + (cc.x >> 5), 1u << (cc.x & 31));
+        if (cc.y != kEmpty32 && cc.y < a.ncorners) atomicOr(a.fbits + (cc.y >> 5), 1u << (cc.y & 31));
+    }
+}
+
+// DETECT (short schedule): this pass is also where the import is PROVEN clean -- it gathers every distinct
+// triplet's 8 floats anyway, so NaN/Inf screening, the bounding box and the value-key insert (which raises
+// has_value_dup when two triplets carry one value) ride along here instead of costing a pass of their own.  The
+// passes before it ran on the assumption "clean"; if the status block says otherwise, vkm_plan_finish re-runs
+// the import with the full schedule (k_resolve_slots first).
+template <bool DETECT>
 __global__ void __launch_bounds__(kThreads, 8) k_write_vertices(ImportArgs a) {
     const uint32_t npairs = a.m1 >> 1;  // one thread per pair of slots, as in k_resolve_slots
     const bool fuse = import_is_clean(a);
     const bool fast = trip_is_fast(a);
-    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npairs; p += gridDim.x * blockDim.x) {
-        const uint2 cc = __ldcs(reinterpret_cast<const uint2*>(a.table1) + p);
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t neutral = 0x80000000u;
+    const uint32_t padded = DETECT ? ((npairs + 31) & ~31u) : npairs;  // whole warps for the box reduction
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < padded; p += gridDim.x * blockDim.x) {
+        uint2 cc = make_uint2(kEmpty32, kEmpty32);
+        if (p < npairs) cc = __ldcs(reinterpret_cast<const uint2*>(a.table1) + p);
+        uint32_t mn[3] = {neutral, neutral, neutral}, mx[3] = {neutral, neutral, neutral};
+        uint32_t bsh = 0xFFFFFFFFu;
+        bool mixed = false;
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
             const uint32_t c = j ? cc.y : cc.x;
@@ -559,6 +582,34 @@ __global__ void __launch_bounds__(kThreads, 8) k_write_vertices(ImportArgs a) {
             const uint4 tr = slot_triplet(a, 2 * p + j, c, fast);
             uint32_t k[8];
             gather_key(a, tr.x, tr.y, tr.z, k);
+            if (DETECT) {
+                bool bad = false;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) bad |= nonfinite_bits(k[i]);
+                uint32_t pmn[3] = {neutral, neutral, neutral}, pmx[3] = {neutral, neutral, neutral};
+#pragma unroll
+                for (int i = 0; i < 3; ++i)
+                    if ((k[i] & 0x7FFFFFFFu) <= 0x7F800000u) pmn[i] = pmx[i] = enc_float(__uint_as_float(k[i]));
+                if (bsh == 0xFFFFFFFFu || bsh == tr.w) {
+                    bsh = tr.w;
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) {
+                        mn[i] = min(mn[i], pmn[i]);
+                        mx[i] = max(mx[i], pmx[i]);
+                    }
+                } else {
+                    mixed = true;
+                    box_atomics(a.ext_enc + 6u * tr.w, pmn, pmx);
+                }
+                if (bad) {
+                    a.status->has_unmatchable = 1;
+                } else {
+                    uint32_t kc[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) kc[i] = canon_bits(k[i]);
+                    insert_value(a, c, kc, tr.w, a.shape_off[tr.w], a.shape_off[tr.w + 1]);
+                }
+            }
             float4 tangent = make_float4(0.f, 0.f, 0.f, 0.f);  // a vertex no triangle references keeps zeros
             const uint32_t lf = fuse ? a.lastface[id] : 0;
             if (lf) {
@@ -577,6 +628,23 @@ __global__ void __launch_bounds__(kThreads, 8) k_write_vertices(ImportArgs a) {
                 tangent = tangent_of(t);
             }
             store_vertex(a.out_vtx + 4ull * id, k, tangent);
+        }
+        if (DETECT) {  // bounding box: one set of (improvement-checked) atomics per warp when its slots share a shape
+            const bool have = (bsh != 0xFFFFFFFFu);
+            const uint32_t any = __ballot_sync(0xFFFFFFFFu, have);
+            if (any) {
+                const uint32_t sh0 = __shfl_sync(0xFFFFFFFFu, bsh, __ffs(any) - 1);
+                if (__all_sync(0xFFFFFFFFu, !have || (bsh == sh0 && !mixed))) {
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) {
+                        mn[i] = __reduce_min_sync(0xFFFFFFFFu, mn[i]);
+                        mx[i] = __reduce_max_sync(0xFFFFFFFFu, mx[i]);
+                    }
+                    if (lane == 0) box_atomics(a.ext_enc + 6u * sh0, mn, mx);
+                } else if (have) {
+                    box_atomics(a.ext_enc + 6u * bsh, mn, mx);
+                }
+            }
         }
     }
 }

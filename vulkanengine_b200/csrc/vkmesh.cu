@@ -253,7 +253,9 @@ int plan_enqueue(vkm_plan* p) {
 #undef VKM_K1
     }
     if (T) CU(cudaEventRecord(ev[PH_VALUES], st));
-    k_resolve_slots<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a, full);
+    // short schedule: the value-level proof rides along in k_write_vertices<true>; only the flag bits are set here
+    if (full) k_resolve_slots<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a, true);
+    else k_flag_firsts<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_SCAN], st));
     if (full) {
         k_redo_flags_clear<<<grid_for(a.nwords, kThreads, dev), kThreads, 0, st>>>(a);
@@ -267,7 +269,8 @@ int plan_enqueue(vkm_plan* p) {
     if (full) k_final_index<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
     k_write_indices<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_VERTICES], st));
-    k_write_vertices<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
+    if (full) k_write_vertices<false><<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
+    else k_write_vertices<true><<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
     if (full) k_write_unmatchable_vertices<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_TANGENTS], st));
     if (full)
