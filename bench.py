@@ -374,11 +374,21 @@ def main():
     torch.cuda.synchronize()
     single_s = max_over_ranks(time.perf_counter() - t0)
     barrier()
+    capi.set_result_memory(1)
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    single_pooled_s = max_over_ranks(time.perf_counter() - t0)
+    capi.set_result_memory(0)
+    barrier()
 
     # The same steps through the batch entry point: every step is one mesh of the batch, its inputs are copied
     # host->device and its results device->host inside the timed region; two lanes per GPU let the copies of one
     # step overlap the kernels / copies of the next.
-    nb = max(args.e2e_steps, 2)
+    nb = max(2 * args.e2e_steps, 2)
     ins = (capi.MeshIn * nb)()
     outs_b = (C_.POINTER(capi.ShapeOut) * nb)()
     arrs = []
@@ -396,21 +406,36 @@ def main():
             for i in range(nshapes):
                 L.vkm_free_shape(C_.byref(arr[i]))
 
-    batch_step()  # warm-up: lanes, plans, pinned staging
-    barrier()
-    t0 = time.perf_counter()
-    batch_step()
-    torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
-    barrier()
+    def timed_batch(result_mode):
+        capi.set_result_memory(result_mode)
+        batch_step()  # warm-up: lanes, plans, pinned staging / result blocks
+        barrier()
+        t0 = time.perf_counter()
+        batch_step()
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        barrier()
+        return dt
+
+    malloc_s = timed_batch(0)
+    e2e_s = timed_batch(1)
+    capi.set_result_memory(0)
     e2e_value = sum_over_ranks(float(F)) * nb / e2e_s
     e2e = {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(mesh.input_bytes()),
            "d2h_bytes_per_step": int(64 * nv + 4 * ni), "ms_per_step": e2e_s / nb * 1e3, "steps": nb,
-           "api": "vkm_import_batch (host pointers; inputs pinned, outputs malloc'd as the engine expects; 2 lanes per "
-                  "GPU overlap one step's copies with the next step's kernels)",
+           "api": "vkm_import_batch (host pointers; inputs page-locked; results in the library's recycled page-locked "
+                  "blocks, vkm_set_result_memory(1), released with vkm_free_shape inside the timed region; 2 lanes per "
+                  "GPU take turns per PCIe direction so one step's upload runs against another step's download)",
+           "malloc_results": {"value": sum_over_ranks(float(F)) * nb / malloc_s, "unit": UNIT,
+                              "ms_per_step": malloc_s / nb * 1e3,
+                              "api": "vkm_import_batch, results malloc()ed per shape as the reference's GeometryConfig "
+                                     "owns them (default mode; one extra host copy out of page-locked staging)"},
            "single_call": {"value": sum_over_ranks(float(F)) * args.e2e_steps / single_s, "unit": UNIT,
                            "ms_per_step": single_s / args.e2e_steps * 1e3,
-                           "api": "vkm_import_shapes, one synchronous call per step"}}
+                           "api": "vkm_import_shapes, one synchronous call per step, malloc()ed results"},
+           "single_call_pooled": {"value": sum_over_ranks(float(F)) * args.e2e_steps / single_pooled_s, "unit": UNIT,
+                                  "ms_per_step": single_pooled_s / args.e2e_steps * 1e3,
+                                  "api": "vkm_import_shapes, one synchronous call per step, page-locked result blocks"}}
     for p in (h_pos, h_nrm, h_uv, h_idx):
         L.vkm_host_free(p)
 

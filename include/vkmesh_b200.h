@@ -95,6 +95,18 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
                       vkm_shape_out* out);
 void vkm_free_shape(vkm_shape_out* shape);
 
+/* Where the host entry points (vkm_import_shapes, vkm_import_batch, vkm_import_obj_text) put their results.
+ *   0 (default): malloc()ed buffers, one pair per shape -- what GeometryConfig owns in the reference
+ *                (Platform::AllocMemory == malloc at mesh_loader.cpp:303-311, released with
+ *                Platform::FrMemory == free at mesh_resource.cpp:13-18).  Costs one host copy out of the page-locked staging.
+ *   1          : page-locked blocks owned by the library and recycled: one block per call, the device writes
+ *                the results into it directly (no staging copy, no page faults).  The buffers MUST then be
+ *                released with vkm_free_shape(), never free(); idle blocks are kept for reuse up to
+ *                VKM_RESULT_POOL_MAX_MB (environment, default 8192) and dropped by vkm_shutdown() or mode 0.
+ * vkm_free_shape() accepts buffers of either kind, so the mode can change while results are outstanding.
+ * No counterpart in the reference (its loader has no device). */
+int vkm_set_result_memory(int mode);
+
 /* A batch of independent meshes (each what one vkm_import_shapes call takes) over every GPU selected with
  * vkm_init(): the multi-GPU form of the same reference loop (each mesh is an independent dedup domain,
  * mesh_loader.cpp:322-324 clears all state between shapes; the reference itself has no multi-mesh entry).  Meshes

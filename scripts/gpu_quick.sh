@@ -9,5 +9,6 @@ d = json.load(open("gpurun_out/bench_quick.json"))
 print("Gtris/s %.3f  ms/step %.4f  pipeline frac %.4f" % (d["value"] / 1e9, d["ms_per_step"], d["pipeline_roofline"]["frac"]))
 print({k: round(v["ms"], 4) for k, v in d["pipeline_roofline"]["kernels"].items()})
 print("roofline", {k: d["roofline"][k] for k in ("achieved", "frac", "traffic")}, "dominant", {k: d["roofline"]["dominant_kernel"][k] for k in ("kernel", "frac", "share_of_step")})
-print("e2e", d["e2e"]["value"] / 1e6, "Mtris/s", d["e2e"]["ms_per_step"], "ms; single", d["e2e"].get("single_call"), d["clocks"])
+e = d["e2e"]
+print("e2e %.1f Mtris/s %.2f ms" % (e["value"] / 1e6, e["ms_per_step"]), {k: round(e[k]["ms_per_step"], 2) for k in ("malloc_results", "single_call", "single_call_pooled") if k in e}, d["clocks"])
 PY

@@ -26,7 +26,7 @@ ERR_NAMES = {1: "INVALID_ARG", 2: "BAD_INDEX", 3: "OOM", 4: "CUDA", 5: "NO_DEVIC
 SYMBOLS = [
     "vkm_device_count", "vkm_init", "vkm_shutdown", "vkm_last_error", "vkm_version",
     "vkm_generate_tangents", "vkm_generate_normals", "vkm_deduplicate_vertices",
-    "vkm_import_shapes", "vkm_free_shape", "vkm_host_alloc", "vkm_host_free", "vkm_import_batch",
+    "vkm_import_shapes", "vkm_free_shape", "vkm_set_result_memory", "vkm_host_alloc", "vkm_host_free", "vkm_import_batch",
     "vkm_e3dm_write", "vkm_e3dm_read", "vkm_e3dm_free", "vkm_parse_obj", "vkm_free_obj_streams",
     "vkm_import_obj_text", "vkm_free_obj_import", "vkm_generate_plane_config", "vkm_generate_cube_config",
     "vkm_plan_create", "vkm_plan_destroy", "vkm_plan_import", "vkm_plan_finish", "vkm_plan_set_timing",
@@ -138,6 +138,8 @@ def lib():
     L.vkm_generate_plane_config.argtypes = [C.c_float, C.c_float, C.c_uint32, C.c_uint32, C.c_float, C.c_float, C.c_int, C.POINTER(ShapeOut)]
     L.vkm_generate_cube_config.restype = C.c_int
     L.vkm_generate_cube_config.argtypes = [C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.POINTER(ShapeOut)]
+    L.vkm_set_result_memory.restype = C.c_int
+    L.vkm_set_result_memory.argtypes = [C.c_int]
     L.vkm_host_alloc.restype = C.c_void_p
     L.vkm_host_alloc.argtypes = [C.c_uint64]
     L.vkm_host_free.argtypes = [C.c_void_p]
@@ -203,6 +205,11 @@ def _copy_out(ptr, nbytes, dtype):
     if not nbytes:
         return np.empty(0, dtype)
     return np.frombuffer((C.c_char * nbytes).from_address(ptr), dtype=dtype).copy()
+
+
+def set_result_memory(mode: int) -> None:
+    """0: malloc()ed results (engine-compatible default); 1: pooled page-locked results (release with vkm_free_shape)."""
+    _check(lib().vkm_set_result_memory(int(mode)))
 
 
 def init(devices=None) -> None:

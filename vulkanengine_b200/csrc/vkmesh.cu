@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -77,6 +78,89 @@ void* malloc_result(uint64_t bytes) {
 #endif
     return p;
 }
+
+// Optional home for the results of the host entry points (vkm_set_result_memory(1)): page-locked blocks that are
+// recycled through vkm_free_shape().  One block holds every buffer of one import call (vertices of all shapes, then
+// indices of all shapes), so the device-to-host leg is two DMA transfers straight into the caller-visible memory:
+// no bounce buffer, no host copy, no first-touch page faults.  Blocks are cudaHostAllocPortable (any device of the
+// process may write them) and are kept for reuse up to `max_idle` bytes.
+struct ResultBlock {
+    char* base = nullptr;
+    uint64_t cap = 0;
+    uint32_t refs = 0;  // caller-visible pointers into the block that have not been released yet
+};
+struct ResultPool {
+    std::mutex mu;
+    std::map<uintptr_t, ResultBlock> live;
+    std::vector<ResultBlock> idle;
+    uint64_t idle_bytes = 0;
+    uint64_t max_idle = 8ull << 30;
+
+    ResultPool() {
+        if (const char* e = getenv("VKM_RESULT_POOL_MAX_MB")) max_idle = strtoull(e, nullptr, 10) << 20;
+    }
+    char* acquire(uint64_t bytes, uint32_t refs) {
+        std::lock_guard<std::mutex> lk(mu);
+        size_t best = idle.size();
+        for (size_t i = 0; i < idle.size(); ++i)
+            if (idle[i].cap >= bytes && (best == idle.size() || idle[i].cap < idle[best].cap)) best = i;
+        ResultBlock b;
+        if (best != idle.size() && idle[best].cap <= 2 * bytes + (4ull << 20)) {
+            b = idle[best];
+            idle[best] = idle.back();
+            idle.pop_back();
+            idle_bytes -= b.cap;
+        } else {
+            b.cap = (bytes + (2ull << 20) - 1) & ~((2ull << 20) - 1);
+            void* q = nullptr;
+            if (cudaHostAlloc(&q, b.cap, cudaHostAllocPortable) != cudaSuccess) {
+                cudaGetLastError();
+                // make room: drop every idle block and try once more
+                for (auto& i : idle) cudaFreeHost(i.base);
+                idle.clear();
+                idle_bytes = 0;
+                if (cudaHostAlloc(&q, b.cap, cudaHostAllocPortable) != cudaSuccess) {
+                    cudaGetLastError();
+                    return nullptr;
+                }
+            }
+            b.base = (char*)q;
+        }
+        b.refs = refs;
+        live[(uintptr_t)b.base] = b;
+        return b.base;
+    }
+    // true when p pointed into a pool block (one reference dropped), false when it is not ours
+    bool release(const void* p, uint32_t n = 1) {
+        if (!p) return false;
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = live.upper_bound((uintptr_t)p);
+        if (it == live.begin()) return false;
+        --it;
+        ResultBlock& b = it->second;
+        if ((uintptr_t)p >= (uintptr_t)b.base + b.cap) return false;
+        b.refs = b.refs > n ? b.refs - n : 0;
+        if (b.refs == 0) {
+            ResultBlock done = b;
+            live.erase(it);
+            if (idle_bytes + done.cap <= max_idle) {
+                idle.push_back(done);
+                idle_bytes += done.cap;
+            } else {
+                cudaFreeHost(done.base);
+            }
+        }
+        return true;
+    }
+    void trim() {
+        std::lock_guard<std::mutex> lk(mu);
+        for (auto& i : idle) cudaFreeHost(i.base);
+        idle.clear();
+        idle_bytes = 0;
+    }
+};
+ResultPool g_results;
+std::atomic<int> g_result_mode{0};  // 0: malloc()ed results, 1: pooled page-locked results
 
 int sm_count(int device) {
     static int cached[64] = {0};
@@ -604,6 +688,17 @@ struct HostCtx {
     uint64_t h_stage_cap = 0;
     std::vector<cudaEvent_t> chunk_ev;
     unsigned copy_threads = 8;  // host threads that move finished chunks into the result buffers
+    // vkm_import_batch: the two lanes of one device take turns on each PCIe direction, so that one lane's upload
+    // runs against the other lane's download (full duplex) instead of both sharing one direction in lock step
+    std::mutex* h2d_gate = nullptr;
+    std::mutex* d2h_gate = nullptr;
+};
+struct Gate {  // lock_guard over an optional mutex
+    std::mutex* m;
+    explicit Gate(std::mutex* mu) : m(mu) { if (m) m->lock(); }
+    ~Gate() { if (m) m->unlock(); }
+    Gate(const Gate&) = delete;
+    Gate& operator=(const Gate&) = delete;
 };
 HostCtx g_ctx;                  // the lane behind the single-call host entry points
 std::mutex g_lanes_mu;
@@ -755,6 +850,7 @@ void vkm_shutdown(void) {
     }
     std::lock_guard<std::mutex> lk(g_ctx.mu);
     release_ctx(g_ctx);
+    g_results.trim();  // idle blocks only; blocks the caller still holds stay valid until vkm_free_shape()
 }
 
 static void release_ctx(HostCtx& c) {
@@ -839,8 +935,9 @@ uint32_t vkm_deduplicate_vertices(uint32_t vc, const void* vertices, uint32_t ic
 
 void vkm_free_shape(vkm_shape_out* s) {
     if (!s) return;
-    free(s->vertices);
-    free(s->indices);
+    // pooled page-locked results go back to the pool, everything else came from malloc()
+    if (!g_results.release(s->vertices)) free(s->vertices);
+    if (!g_results.release(s->indices)) free(s->indices);
     s->vertices = nullptr;
     s->indices = nullptr;
 }
@@ -870,6 +967,36 @@ static int import_resident(HostCtx& c, const float* d_pos, uint64_t np, const fl
     if ((rc = vkm_plan_finish(c.plan, &r))) return rc;
     tr.mark("H2D + kernels (finish)");
     const uint64_t vbytes = r.total_vertices * 64, ibytes = C * 4;
+    if (g_result_mode.load() == 1) {
+        // one page-locked block: [vertices of every shape][indices of every shape], DMA'd in place
+        char* base = g_results.acquire(vbytes + ibytes + 64, 2 * nshapes);
+        if (!base) return fail(VKM_ERR_OOM, "vkm_import_shapes: page-locked result block (%llu bytes) could not be allocated",
+                               (unsigned long long)(vbytes + ibytes + 64));
+        for (uint32_t s = 0; s < nshapes; ++s) {
+            vkm_shape_out& o = out[s];
+            const uint32_t v0 = r.shape_vertex_offsets[s], v1 = r.shape_vertex_offsets[s + 1];
+            o.vertex_count = v1 - v0;
+            o.index_count = (uint32_t)(shape_off[s + 1] - shape_off[s]);
+            o.extent = r.shape_extents[s];
+            o.vertices = base + (uint64_t)v0 * 64;
+            o.indices = base + vbytes + shape_off[s] * 4;
+        }
+        tr.mark("result block");
+        cudaError_t e = cudaSuccess;
+        {
+            Gate g(c.d2h_gate);
+            if (vbytes) e = cudaMemcpyAsync(base, r.d_vertices, vbytes, cudaMemcpyDeviceToHost, c.st);
+            if (e == cudaSuccess && ibytes) e = cudaMemcpyAsync(base + vbytes, r.d_indices, ibytes, cudaMemcpyDeviceToHost, c.st);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(c.st);
+        }
+        if (e != cudaSuccess) {
+            g_results.release(base, 2 * nshapes);
+            for (uint32_t k = 0; k < nshapes; ++k) out[k].vertices = out[k].indices = nullptr;
+            return fail(VKM_ERR_CUDA, "device-to-host copy failed: %s", cudaGetErrorString(e));
+        }
+        tr.mark("D2H (in place)");
+        return VKM_OK;
+    }
     std::vector<Seg> segs;
     segs.reserve(2ull * nshapes);
     for (uint32_t s = 0; s < nshapes; ++s) {
@@ -890,7 +1017,11 @@ static int import_resident(HostCtx& c, const float* d_pos, uint64_t np, const fl
     for (uint32_t s = 0; s < nshapes; ++s)
         if (out[s].index_count) segs.push_back(Seg{vbytes + shape_off[s] * 4, (char*)out[s].indices, (uint64_t)out[s].index_count * 4});
     tr.mark("malloc results");
-    if ((rc = download_staged(c, r.d_vertices, vbytes, r.d_indices, ibytes, segs))) {
+    {
+        Gate g(c.d2h_gate);
+        rc = download_staged(c, r.d_vertices, vbytes, r.d_indices, ibytes, segs);
+    }
+    if (rc) {
         for (uint32_t k = 0; k < nshapes; ++k) vkm_free_shape(&out[k]);
         return rc;
     }
@@ -923,10 +1054,14 @@ static int lane_import(HostCtx& c, const float* pos, uint64_t np, const float* n
     if ((rc = c.nrm.ensure(3 * nn + 4))) return rc;
     if ((rc = c.uv.ensure(2 * nt + 4))) return rc;
     if ((rc = c.idx.ensure(3 * C + 16))) return rc;
-    if (np) CU(cudaMemcpyAsync(c.pos.p, pos, np * 12, cudaMemcpyHostToDevice, c.st));
-    if (nn) CU(cudaMemcpyAsync(c.nrm.p, nrm, nn * 12, cudaMemcpyHostToDevice, c.st));
-    if (nt) CU(cudaMemcpyAsync(c.uv.p, uv, nt * 8, cudaMemcpyHostToDevice, c.st));
-    if (C) CU(cudaMemcpyAsync(c.idx.p, idx, C * 12, cudaMemcpyHostToDevice, c.st));
+    {
+        Gate g(c.h2d_gate);
+        if (np) CU(cudaMemcpyAsync(c.pos.p, pos, np * 12, cudaMemcpyHostToDevice, c.st));
+        if (nn) CU(cudaMemcpyAsync(c.nrm.p, nrm, nn * 12, cudaMemcpyHostToDevice, c.st));
+        if (nt) CU(cudaMemcpyAsync(c.uv.p, uv, nt * 8, cudaMemcpyHostToDevice, c.st));
+        if (C) CU(cudaMemcpyAsync(c.idx.p, idx, C * 12, cudaMemcpyHostToDevice, c.st));
+        if (c.h2d_gate) CU(cudaStreamSynchronize(c.st));  // hold the direction until the upload has landed
+    }
     tr.mark("enqueue H2D");
     return import_resident(c, c.pos.p, np, c.nrm.p, nn, c.uv.p, nt, c.idx.p, shape_off, nshapes, out, tr);
 }
@@ -955,9 +1090,14 @@ int vkm_import_batch(const vkm_mesh_in* meshes, uint32_t count, vkm_shape_out* c
     const size_t nd = devices.size();
     std::lock_guard<std::mutex> batch_lock(g_lanes_mu);  // one batch at a time
     while (g_lanes.size() < 2 * nd) g_lanes.push_back(new HostCtx());
+    std::vector<std::mutex> gates(2 * nd);
     for (size_t k = 0; k < 2 * nd; ++k) {
         g_lanes[k]->devices[0] = devices[k / 2];
         g_lanes[k]->copy_threads = 8;
+        // (with malloc()ed results the download leg is mostly host copying, which overlaps better ungated)
+        const bool gated = g_result_mode.load() == 1;
+        g_lanes[k]->h2d_gate = gated ? &gates[2 * (k / 2)] : nullptr;
+        g_lanes[k]->d2h_gate = gated ? &gates[2 * (k / 2) + 1] : nullptr;
     }
     // LPT partition by corner count (deterministic: ties by mesh id)
     std::vector<uint32_t> order(count);
@@ -993,6 +1133,7 @@ int vkm_import_batch(const vkm_mesh_in* meshes, uint32_t count, vkm_shape_out* c
     for (size_t lane = 1; lane < 2 * nd; ++lane) pool.emplace_back(work, lane);
     work(0);
     for (auto& t : pool) t.join();
+    for (size_t k = 0; k < 2 * nd; ++k) g_lanes[k]->h2d_gate = g_lanes[k]->d2h_gate = nullptr;
     int rc = VKM_OK;
     for (uint32_t i = 0; i < count; ++i) {
         if (statuses) statuses[i] = st[i];
@@ -1018,6 +1159,13 @@ int vkm_internal_import_device(int device, const float* d_pos, uint64_t np, cons
     int rc = ctx_bind(c);
     if (rc) return rc;
     return import_resident(c, d_pos, np, d_nrm, nn, d_uv, nt, d_idx, shape_off, nshapes, out, tr);
+}
+
+int vkm_set_result_memory(int mode) {
+    if (mode != 0 && mode != 1) return fail(VKM_ERR_INVALID_ARG, "vkm_set_result_memory: mode must be 0 (malloc) or 1 (pooled page-locked)");
+    g_result_mode.store(mode);
+    if (mode == 0) g_results.trim();
+    return VKM_OK;
 }
 
 void* vkm_host_alloc(uint64_t bytes) {
