@@ -102,7 +102,7 @@ void vkm_free_shape(vkm_shape_out* shape);
  *   1          : page-locked blocks owned by the library and recycled: one block per call, the device writes
  *                the results into it directly (no staging copy, no page faults).  The buffers MUST then be
  *                released with vkm_free_shape(), never free(); idle blocks are kept for reuse up to
- *                VKM_RESULT_POOL_MAX_MB (environment, default 8192) and dropped by vkm_shutdown() or mode 0.
+ *                VKM_RESULT_POOL_MAX_MB (environment; default a quarter of host memory, at least 8192) and dropped by vkm_shutdown() or mode 0.
  * vkm_free_shape() accepts buffers of either kind, so the mode can change while results are outstanding.
  * No counterpart in the reference (its loader has no device). */
 int vkm_set_result_memory(int mode);

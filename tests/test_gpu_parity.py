@@ -486,3 +486,31 @@ def test_config5_adversarial_64m_properties():
     out = gpu_of(m)[0]
     assert len(out.vertices) < (1 << 26)  # the reference's own u32 byte-size limit (mesh_loader.cpp:301)
     _check_import_properties(m, out, sample=3_000_000)
+
+
+def test_host_plan_grows_when_vertices_outnumber_attribute_records():
+    """The host entry points size the vertex buffer from the attribute arrays; a mesh that combines few records into
+    many distinct corners (here 20 x 20 x 20 = 8000 vertices from 20-record arrays) makes the plan re-run with the
+    reported count instead of failing with VKM_ERR_CAPACITY."""
+    rng = np.random.default_rng(77)
+    k = 20
+    pos = rng.standard_normal((k, 3)).astype(np.float32)
+    nrm = rng.standard_normal((k, 3)).astype(np.float32)
+    uv = rng.random((k, 2)).astype(np.float32)
+    combos = np.stack(np.meshgrid(np.arange(k), np.arange(k), np.arange(k), indexing="ij"), -1).reshape(-1, 3)
+    combos = combos[rng.permutation(len(combos))]
+    idx = np.concatenate([combos, combos[rng.integers(0, len(combos), 4000)]]).astype(np.int32)
+    idx = idx[: len(idx) // 3 * 3]
+    so = np.array([0, len(idx)], np.uint64)
+    capi.shutdown()  # drop the cached host plan: the next call sizes a fresh one for this mesh
+    for mode in (0, 1):
+        capi.set_result_memory(mode)
+        try:
+            got = capi.import_shapes(pos, nrm, uv, idx, so)
+        finally:
+            capi.set_result_memory(0)
+        assert got[0].vertices.shape[0] == k ** 3
+        assert_shapes_equal(got, port.import_arrays(pos, nrm, uv, idx, so))
+    # and the grown plan keeps serving smaller meshes
+    g = synth.grid(12)
+    assert_shapes_equal(gpu_of(g), oracle_of(g))

@@ -212,6 +212,11 @@ def set_result_memory(mode: int) -> None:
     _check(lib().vkm_set_result_memory(int(mode)))
 
 
+def shutdown() -> None:
+    """vkm_shutdown: release the cached host-entry state (plans, staging, idle result blocks); the next call re-creates it."""
+    lib().vkm_shutdown()
+
+
 def init(devices=None) -> None:
     if devices is None:
         _check(lib().vkm_init(None, 0))

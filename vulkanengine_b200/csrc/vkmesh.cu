@@ -97,6 +97,9 @@ struct ResultPool {
     uint64_t max_idle = 8ull << 30;
 
     ResultPool() {
+        // default: a quarter of the machine's memory, at least 8 GiB
+        const long pages = sysconf(_SC_PHYS_PAGES), psz = sysconf(_SC_PAGESIZE);
+        if (pages > 0 && psz > 0) max_idle = std::max<uint64_t>(max_idle, (uint64_t)pages * (uint64_t)psz / 4);
         if (const char* e = getenv("VKM_RESULT_POOL_MAX_MB")) max_idle = strtoull(e, nullptr, 10) << 20;
     }
     char* acquire(uint64_t bytes, uint32_t refs) {
@@ -239,6 +242,7 @@ struct vkm_plan {
     cudaEvent_t done = nullptr;
     bool timing = false;
     bool pending = false;
+    bool grow_vertices = false;  // on "vertex capacity exceeded": reallocate to the reported count and re-run
     // last import (kept for the re-run after a table overflow)
     ImportArgs args{};
     std::vector<uint32_t> vertex_offsets;
@@ -540,6 +544,20 @@ int vkm_plan_finish(vkm_plan* p, vkm_plan_result* r) {
             continue;
         }
         p->assume_clean = !dirty;
+        if (s.capacity_exceeded && p->grow_vertices && attempt <= 12) {
+            // the host entry points size the vertex buffer from the attribute arrays (an estimate): the status block
+            // carries the true count, so allocate that and run the import once more
+            CU(cudaStreamSynchronize(p->last_stream));
+            const uint64_t want = std::min<uint64_t>(p->args.ncorners, (uint64_t)s.total_vertices + s.total_vertices / 16 + 64);
+            int rc;
+            if ((rc = p->lastface.ensure(want)) || (rc = p->out_vtx.ensure(want * 4))) return rc;
+            p->desc.max_vertices = want;
+            p->args.lastface = p->lastface.p;
+            p->args.out_vtx = p->out_vtx.p;
+            p->args.vertex_capacity = (uint32_t)std::min<uint64_t>(want, 0xFFFFFFFEull);
+            if ((rc = plan_enqueue(p))) return rc;
+            continue;
+        }
         if (s.capacity_exceeded) return fail(VKM_ERR_CAPACITY, "import: %u unique vertices exceed the plan capacity %llu", s.total_vertices, (unsigned long long)p->desc.max_vertices);
         break;
     }
@@ -956,10 +974,12 @@ static int import_resident(HostCtx& c, const float* d_pos, uint64_t np, const fl
         vkm_plan_desc d{};
         d.device = c.devices[0];
         d.max_corners = C;
-        d.max_vertices = 0;
+        // unique vertices are usually close to the largest attribute array; the plan grows when they are not
+        d.max_vertices = std::min<uint64_t>(C, max_attrib + max_attrib / 8 + 1024);
         d.max_attrib = max_attrib;
         d.max_shapes = nshapes;
         if ((rc = vkm_plan_create(&d, &c.plan))) return rc;
+        c.plan->grow_vertices = true;
     }
     c.plan->t1_mode = 0;  // every host call is a new mesh: try the coherent addressing first
     if ((rc = vkm_plan_import(c.plan, d_pos, np, d_nrm, nn, d_uv, nt, d_idx, shape_off, nshapes, c.st))) return rc;
