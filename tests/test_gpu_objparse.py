@@ -158,3 +158,20 @@ def test_import_obj_text_equals_reference_loadobj(tmp_path):
         got, names, mats = capi.import_obj_text(text.encode())
         assert_shapes_equal(got, want)
         assert names == [w.name for w in want]
+
+
+def test_cached_parser_state_across_sizes_and_shutdown(tmp_path):
+    """The parser keeps its device buffers, stream and staging between calls: a large file (above the staged-upload
+    threshold), then small ones, then the large one again, with a vkm_shutdown in between, all match tinyobj."""
+    big = synth.to_obj_text(synth.grid(260))          # about 15 MB of text: uploaded through the page-locked staging
+    small = synth.to_obj_text(synth.uv_sphere(6, 9))
+    tiny = "v 0 0 0\nv 1 0 0\nv 0 1 0\nvt 0 0\nvn 0 0 1\nf 1/1/1 2/1/1 3/1/1\n"
+    for i, text in enumerate([big, small, tiny, big]):
+        compare(text, tmp_path, f"c{i}")
+        if i == 1:
+            capi.shutdown()
+    got, _, _ = capi.import_obj_text(big.encode())
+    m = synth.grid(260)
+    from oracle import port
+    from conftest import assert_shapes_equal
+    assert_shapes_equal(got, port.import_arrays(m.pos, m.nrm, m.uv, m.idx, m.shape_offsets))

@@ -24,12 +24,15 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 extern "C" void vkm_internal_set_error(const char* msg);  // vkmesh.cu: feeds vkm_last_error()
@@ -489,11 +492,127 @@ __global__ void k_parse_faces(const char* __restrict__ text, uint64_t len, const
         }                                                                               \
     } while (0)
 
+// Device buffers, stream, number tables and the page-locked upload staging are kept between calls (a loader parses
+// many files): allocation and release cost more than the parse itself (measured 13-27 ms of cudaFree alone per
+// 116 MB file).  One parse at a time per process; vkm_shutdown() releases everything.
+struct GrowBuf {
+    void* p = nullptr;
+    uint64_t cap = 0;
+    cudaError_t ensure(uint64_t bytes) {
+        if (p && bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        const uint64_t want = bytes + bytes / 8 + 256;  // headroom: the next file of about this size reuses the buffer
+        const cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) {
+            p = nullptr;
+            return e;
+        }
+        cap = want;
+        return cudaSuccess;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+struct ParseCtx {
+    std::mutex mu;
+    int device = -1;
+    cudaStream_t st = nullptr;
+    GrowBuf text, bits, bpre, sums, tot, ls, kind, cnt, off, pos, nrm, uv, idx, sp, status, p10, p5;
+    bool tables_ready = false;
+    char* h_stage = nullptr;
+    uint64_t h_stage_cap = 0;
+
+    void release() {
+        if (device < 0) return;
+        cudaSetDevice(device);
+        for (GrowBuf* b : {&text, &bits, &bpre, &sums, &tot, &ls, &kind, &cnt, &off, &pos, &nrm, &uv, &idx, &sp, &status, &p10, &p5})
+            b->release();
+        if (h_stage) cudaFreeHost(h_stage);
+        h_stage = nullptr;
+        h_stage_cap = 0;
+        if (st) cudaStreamDestroy(st);
+        st = nullptr;
+        tables_ready = false;
+        device = -1;
+    }
+    cudaError_t bind(int dev) {
+        if (device == dev) return cudaSetDevice(dev);
+        release();
+        cudaError_t e = cudaSetDevice(dev);
+        if (e != cudaSuccess) return e;
+        e = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking);
+        if (e != cudaSuccess) return e;
+        device = dev;
+        return cudaSuccess;
+    }
+};
+ParseCtx g_parse;
+
+// Text upload.  The caller's buffer is pageable (a file read into memory): a direct copy goes through the driver's
+// own bounce buffer on one thread.  Instead a few host threads copy 4 MiB pieces into page-locked staging and queue
+// each piece's DMA as soon as it is staged, so staging and transfer overlap.
+cudaError_t upload_text(ParseCtx& c, char* d_text, const char* text, uint64_t len) {
+    constexpr uint64_t kPiece = 4ull << 20, kWindow = 1ull << 30;
+    if (len < kPiece) return len ? cudaMemcpyAsync(d_text, text, len, cudaMemcpyHostToDevice, c.st) : cudaSuccess;
+    const uint64_t window = std::min(len, kWindow);
+    if (c.h_stage_cap < window) {
+        if (c.h_stage) cudaFreeHost(c.h_stage);
+        c.h_stage = nullptr;
+        c.h_stage_cap = 0;
+        if (cudaMallocHost((void**)&c.h_stage, window + window / 8) != cudaSuccess) {
+            cudaGetLastError();  // no page-locked memory to be had: plain copy
+            return cudaMemcpyAsync(d_text, text, len, cudaMemcpyHostToDevice, c.st);
+        }
+        c.h_stage_cap = window + window / 8;
+    }
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    for (uint64_t w0 = 0; w0 < len; w0 += window) {
+        const uint64_t n = std::min(window, len - w0);
+        const uint64_t npieces = (n + kPiece - 1) / kPiece;
+        const unsigned nthreads = (unsigned)std::min<uint64_t>(std::min(8u, hw), npieces);
+        std::atomic<uint64_t> next{0};
+        std::atomic<int> err{(int)cudaSuccess};
+        auto work = [&]() {
+            cudaSetDevice(c.device);
+            for (;;) {
+                const uint64_t k = next.fetch_add(1);
+                if (k >= npieces) return;
+                const uint64_t a = k * kPiece, b = std::min(n, a + kPiece);
+                memcpy(c.h_stage + a, text + w0 + a, b - a);
+                const cudaError_t e = cudaMemcpyAsync(d_text + w0 + a, c.h_stage + a, b - a, cudaMemcpyHostToDevice, c.st);
+                if (e != cudaSuccess) err.store((int)e);
+            }
+        };
+        std::vector<std::thread> pool;
+        for (unsigned t = 1; t < nthreads; ++t) pool.emplace_back(work);
+        work();
+        for (auto& th : pool) th.join();
+        if (err.load() != (int)cudaSuccess) return (cudaError_t)err.load();
+        if (w0 + window < len) {  // the staging is reused by the next window
+            const cudaError_t e = cudaStreamSynchronize(c.st);
+            if (e != cudaSuccess) return e;
+        }
+    }
+    return cudaSuccess;
+}
+
 unsigned grid_of(uint64_t n) { return (unsigned)std::max<uint64_t>(1, std::min<uint64_t>((n + kT - 1) / kT, 148 * 8)); }
 
 }  // namespace
 
 extern "C" {
+
+// vkm_shutdown() (vkmesh.cu) calls this: the parser's cached device buffers, stream and staging.
+void vkm_internal_objparse_release(void) {
+    std::lock_guard<std::mutex> lk(g_parse.mu);
+    g_parse.release();
+}
 
 void vkm_free_obj_streams(vkm_obj_streams* s) {
     if (!s) return;
@@ -520,12 +639,9 @@ static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_stream
     }
     int rc = VKM_OK;
     PTrace ptr;
-    // pow tables from the host libm: the same doubles tinyobj's std::pow calls produce on this machine
+    ParseCtx& c = g_parse;
+    std::lock_guard<std::mutex> parse_lock(c.mu);
     constexpr int kP10 = 400, kBias = 1100;
-    std::vector<double> h_p10(kP10), h_p5(2 * kBias + 1);
-    static const double lut[8] = {1.0, 0.1, 0.01, 0.001, 0.0001, 0.00001, 0.000001, 0.0000001};
-    for (int k = 0; k < kP10; ++k) h_p10[k] = k < 8 ? lut[k] : std::pow(10.0, -k);
-    for (int e = -kBias; e <= kBias; ++e) h_p5[e + kBias] = std::pow(5.0, e);
 
     char* d_text = nullptr;
     uint32_t *d_bits = nullptr, *d_bpre = nullptr, *d_sums = nullptr, *d_tot = nullptr, *d_ls = nullptr, *d_cnt = nullptr,
@@ -544,19 +660,33 @@ static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_stream
     const uint32_t nt1 = std::max<uint32_t>(1, (nwords + kSTile - 1) / kSTile);
     cudaStream_t st = nullptr;
 
+    PCU(c.bind(device));
+    st = c.st;
+    if (!c.tables_ready) {
+        // pow tables from the host libm: the same doubles tinyobj's std::pow calls produce on this machine
+        std::vector<double> h_p10(kP10), h_p5(2 * kBias + 1);
+        static const double lut[8] = {1.0, 0.1, 0.01, 0.001, 0.0001, 0.00001, 0.000001, 0.0000001};
+        for (int k = 0; k < kP10; ++k) h_p10[k] = k < 8 ? lut[k] : std::pow(10.0, -k);
+        for (int e = -kBias; e <= kBias; ++e) h_p5[e + kBias] = std::pow(5.0, e);
+        PCU(c.p10.ensure(sizeof(double) * kP10));
+        PCU(c.p5.ensure(sizeof(double) * (2 * kBias + 1)));
+        PCU(cudaMemcpyAsync(c.p10.p, h_p10.data(), sizeof(double) * kP10, cudaMemcpyHostToDevice, st));
+        PCU(cudaMemcpyAsync(c.p5.p, h_p5.data(), sizeof(double) * (2 * kBias + 1), cudaMemcpyHostToDevice, st));
+        PCU(cudaStreamSynchronize(st));  // the host vectors go out of scope
+        c.tables_ready = true;
+    }
+    d_p10 = (double*)c.p10.p;
+    d_p5 = (double*)c.p5.p;
     ptr.mark("pow tables");
-    PCU(cudaSetDevice(device));
-    PCU(cudaMalloc(&d_text, len + 1));
-    PCU(cudaMalloc(&d_bits, (uint64_t)(nwords + 1) * 4));
-    PCU(cudaMalloc(&d_bpre, (uint64_t)(nwords + 1) * 4));
-    PCU(cudaMalloc(&d_sums, (uint64_t)nt1 * 4 + 64));
-    PCU(cudaMalloc(&d_tot, 64));
-    PCU(cudaMalloc(&d_p10, sizeof(double) * kP10));
-    PCU(cudaMalloc(&d_p5, sizeof(double) * (2 * kBias + 1)));
-    PCU(cudaMalloc(&d_st, sizeof(ParseStatus)));
-    PCU(cudaMemcpyAsync(d_text, text, len, cudaMemcpyHostToDevice, st));
-    PCU(cudaMemcpyAsync(d_p10, h_p10.data(), sizeof(double) * kP10, cudaMemcpyHostToDevice, st));
-    PCU(cudaMemcpyAsync(d_p5, h_p5.data(), sizeof(double) * (2 * kBias + 1), cudaMemcpyHostToDevice, st));
+    PCU(c.text.ensure(len + 1));
+    PCU(c.bits.ensure((uint64_t)(nwords + 1) * 4));
+    PCU(c.bpre.ensure((uint64_t)(nwords + 1) * 4));
+    PCU(c.sums.ensure((uint64_t)nt1 * 4 + 64));
+    PCU(c.tot.ensure(64));
+    PCU(c.status.ensure(sizeof(ParseStatus)));
+    d_text = (char*)c.text.p; d_bits = (uint32_t*)c.bits.p; d_bpre = (uint32_t*)c.bpre.p; d_sums = (uint32_t*)c.sums.p;
+    d_tot = (uint32_t*)c.tot.p; d_st = (ParseStatus*)c.status.p;
+    PCU(upload_text(c, d_text, text, len));
     hst.first_bad_line = 0xFFFFFFFFu;
     PCU(cudaMemcpyAsync(d_st, &hst, sizeof hst, cudaMemcpyHostToDevice, st));
     if (len) {
@@ -570,13 +700,13 @@ static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_stream
     if (nlines) {
         const uint64_t L = nlines;
         const uint32_t nt2 = std::max<uint32_t>(1, (nlines + kSTile - 1) / kSTile);
-        PCU(cudaMalloc(&d_ls, L * 4));
-        PCU(cudaMalloc(&d_kind, L));
-        PCU(cudaMalloc(&d_cnt, L * 4 * 5));
-        PCU(cudaMalloc(&d_off, L * 4 * 5));
-        cudaFree(d_sums);
-        d_sums = nullptr;
-        PCU(cudaMalloc(&d_sums, (uint64_t)nt2 * 4 * 5 + 64));
+        PCU(c.ls.ensure(L * 4));
+        PCU(c.kind.ensure(L));
+        PCU(c.cnt.ensure(L * 4 * 5));
+        PCU(c.off.ensure(L * 4 * 5));
+        PCU(c.sums.ensure((uint64_t)nt2 * 4 * 5 + 64));  // (the line scan has finished with it: stream synchronised above)
+        d_ls = (uint32_t*)c.ls.p; d_kind = (uint8_t*)c.kind.p; d_cnt = (uint32_t*)c.cnt.p; d_off = (uint32_t*)c.off.p;
+        d_sums = (uint32_t*)c.sums.p;
         k_line_starts<<<grid_of(nwords), kT, 0, st>>>(d_bits, d_bpre, nwords, d_ls);
         k_classify<<<grid_of(nlines), kT, 0, st>>>(d_text, len, d_ls, nlines, d_kind, d_cnt, L, d_st);
         k_scan_sum<<<dim3(nt2, 5), kST, 0, st>>>(d_cnt, L, nlines, d_sums, nt2, false);
@@ -590,11 +720,13 @@ static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_stream
             rc = VKM_ERR_UNSUPPORTED;
             goto done;
         }
-        PCU(cudaMalloc(&d_pos, std::max<uint64_t>(1, (uint64_t)tot[0] * 12)));
-        PCU(cudaMalloc(&d_nrm, std::max<uint64_t>(1, (uint64_t)tot[1] * 12)));
-        PCU(cudaMalloc(&d_uv, std::max<uint64_t>(1, (uint64_t)tot[2] * 8)));
-        PCU(cudaMalloc(&d_idx, std::max<uint64_t>(1, (uint64_t)tot[3] * 36)));
-        PCU(cudaMalloc(&d_sp, std::max<uint64_t>(1, (uint64_t)tot[4] * 8)));
+        PCU(c.pos.ensure((uint64_t)tot[0] * 12 + 16));
+        PCU(c.nrm.ensure((uint64_t)tot[1] * 12 + 16));
+        PCU(c.uv.ensure((uint64_t)tot[2] * 8 + 16));
+        PCU(c.idx.ensure((uint64_t)tot[3] * 36 + 64));
+        PCU(c.sp.ensure((uint64_t)tot[4] * 8 + 8));
+        d_pos = (float*)c.pos.p; d_nrm = (float*)c.nrm.p; d_uv = (float*)c.uv.p; d_idx = (int32_t*)c.idx.p;
+        d_sp = (uint2*)c.sp.p;
         k_parse_records<<<grid_of(nlines), kT, 0, st>>>(d_text, len, d_ls, nlines, d_kind, d_off, L, d_pos, d_nrm, d_uv, d_sp,
                                                         d_p10, d_p5, kBias);
         k_parse_faces<<<grid_of(nlines), kT, 0, st>>>(d_text, len, d_ls, nlines, d_kind, d_off, L, d_pos, tot[0], d_idx, d_st);
@@ -704,10 +836,7 @@ static int parse_impl(int device, const char* text, uint64_t len, vkm_obj_stream
     }
 done:
     ptr.mark("shapes / import");
-    cudaFree(d_text); cudaFree(d_bits); cudaFree(d_bpre); cudaFree(d_sums); cudaFree(d_tot); cudaFree(d_ls);
-    cudaFree(d_cnt); cudaFree(d_off); cudaFree(d_kind); cudaFree(d_p10); cudaFree(d_p5); cudaFree(d_pos);
-    cudaFree(d_nrm); cudaFree(d_uv); cudaFree(d_idx); cudaFree(d_sp); cudaFree(d_st);
-    ptr.mark("cudaFree");
+    if (rc != VKM_OK && st) cudaStreamSynchronize(st);  // nothing of this call may still be running on the cached buffers
     if (rc != VKM_OK) vkm_free_obj_streams(out);
     return rc;
 }

@@ -857,6 +857,7 @@ int vkm_init(const int* device_ordinals, int count) {
 }
 
 static void release_ctx(HostCtx& c);
+void vkm_internal_objparse_release(void);  // vkm_objparse.cu
 
 void vkm_shutdown(void) {
     {
@@ -868,6 +869,7 @@ void vkm_shutdown(void) {
     }
     std::lock_guard<std::mutex> lk(g_ctx.mu);
     release_ctx(g_ctx);
+    vkm_internal_objparse_release();
     g_results.trim();  // idle blocks only; blocks the caller still holds stay valid until vkm_free_shape()
 }
 
