@@ -385,6 +385,23 @@ def main():
         e2e_step()
     torch.cuda.synchronize()
     single_pooled_s = max_over_ranks(time.perf_counter() - t0)
+
+    # the same call on PAGEABLE inputs (numpy arrays: what a drop-in caller holding tinyobj's vectors has)
+    def pageable_step():
+        rc = L.vkm_import_shapes(mesh.pos.ctypes.data, len(mesh.pos), mesh.nrm.ctypes.data, len(mesh.nrm),
+                                 mesh.uv.ctypes.data, len(mesh.uv), mesh.idx.ctypes.data, so.ctypes.data, nshapes, out)
+        if rc:
+            raise SystemExit("vkm_import_shapes failed: " + L.vkm_last_error().decode())
+        for i in range(nshapes):
+            L.vkm_free_shape(C_.byref(out[i]))
+
+    pageable_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        pageable_step()
+    torch.cuda.synchronize()
+    pageable_s = max_over_ranks(time.perf_counter() - t0)
     capi.set_result_memory(0)
     barrier()
 
@@ -441,7 +458,11 @@ def main():
                            "api": "vkm_import_shapes, one synchronous call per step, malloc()ed results"},
            "single_call_pooled": {"value": sum_over_ranks(float(F)) * args.e2e_steps / single_pooled_s, "unit": UNIT,
                                   "ms_per_step": single_pooled_s / args.e2e_steps * 1e3,
-                                  "api": "vkm_import_shapes, one synchronous call per step, page-locked result blocks"}}
+                                  "api": "vkm_import_shapes, one synchronous call per step, page-locked result blocks"},
+           "single_call_pageable_inputs": {"value": sum_over_ranks(float(F)) * args.e2e_steps / pageable_s, "unit": UNIT,
+                                           "ms_per_step": pageable_s / args.e2e_steps * 1e3,
+                                           "api": "as single_call_pooled, inputs in ordinary pageable memory (staged "
+                                                  "through the library's page-locked ring by copy threads)"}}
     for p in (h_pos, h_nrm, h_uv, h_idx):
         L.vkm_host_free(p)
 

@@ -710,7 +710,16 @@ struct HostCtx {
     // runs against the other lane's download (full duplex) instead of both sharing one direction in lock step
     std::mutex* h2d_gate = nullptr;
     std::mutex* d2h_gate = nullptr;
+    // page-locked ring for uploads from pageable caller memory (the engine's std::vector storage): kUpSlots pieces
+    static constexpr uint64_t kUpPiece = 4ull << 20;
+    static constexpr unsigned kUpSlots = 32;
+    char* h_up = nullptr;
+    std::vector<cudaEvent_t> up_ev;
+    uint64_t up_issued = 0;                    // pieces queued so far, over all calls (piece g uses slot g % kUpSlots)
+    std::atomic<uint64_t> up_done[kUpSlots]{};  // per slot: 1 + the last piece whose DMA and event have been queued
 };
+constexpr uint64_t kUpPiece = HostCtx::kUpPiece;
+constexpr unsigned kUpSlots = HostCtx::kUpSlots;
 struct Gate {  // lock_guard over an optional mutex
     std::mutex* m;
     explicit Gate(std::mutex* mu) : m(mu) { if (m) m->lock(); }
@@ -798,6 +807,86 @@ int download_staged(HostCtx& c, const void* d_vertices, uint64_t vbytes, const v
     return VKM_OK;
 }
 
+void release_upload_ring(HostCtx& c) {
+    if (c.h_up) cudaFreeHost(c.h_up);
+    c.h_up = nullptr;
+    for (auto e : c.up_ev) cudaEventDestroy(e);
+    c.up_ev.clear();
+    c.up_issued = 0;
+    for (auto& d : c.up_done) d.store(0);
+}
+
+bool is_page_locked(const void* p) {
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
+}
+
+// Host-to-device copy of one input stream.  Page-locked sources go straight to the copy engine.  Pageable sources
+// (what a drop-in caller has: tinyobj's vectors) would be bounced by the driver on one thread at a few GB/s; here a
+// few host threads copy 4 MiB pieces into a page-locked ring and queue each piece's DMA as soon as it is staged.
+// A ring slot is reused once the DMA that last read it has completed (per-slot event + sequence number).
+int upload_stream(HostCtx& c, void* dst, const void* src, uint64_t bytes) {
+    if (bytes == 0) return VKM_OK;
+    if (bytes < 2 * kUpPiece || is_page_locked(src)) {
+        CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.st));
+        return VKM_OK;
+    }
+    if (!c.h_up) {
+        if (cudaMallocHost((void**)&c.h_up, kUpPiece * kUpSlots) != cudaSuccess) {
+            cudaGetLastError();
+            c.h_up = nullptr;
+            CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.st));  // no page-locked memory: plain copy
+            return VKM_OK;
+        }
+        for (unsigned i = 0; i < kUpSlots; ++i) {
+            cudaEvent_t e;
+            CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            c.up_ev.push_back(e);
+        }
+    }
+    const uint64_t npieces = (bytes + kUpPiece - 1) / kUpPiece;
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const unsigned nthreads = (unsigned)std::min<uint64_t>(std::min(std::max(1u, c.copy_threads), hw), npieces);
+    std::atomic<uint64_t> next{0};
+    std::atomic<int> err{0};
+    const uint64_t base = c.up_issued;
+    const int dev = c.bound_device;
+    auto work = [&]() {
+        cudaSetDevice(dev);
+        for (;;) {
+            const uint64_t k = next.fetch_add(1);
+            if (k >= npieces) return;
+            const uint64_t g = base + k;
+            const unsigned slot = (unsigned)(g % kUpSlots);
+            if (g >= kUpSlots) {
+                // the slot's previous user (piece g - kUpSlots, possibly of an earlier call) has queued its DMA ...
+                while (c.up_done[slot].load(std::memory_order_acquire) < g - kUpSlots + 1) std::this_thread::yield();
+                // ... and that DMA has finished reading the slot
+                if (cudaEventSynchronize(c.up_ev[slot]) != cudaSuccess) err.store(1);
+            }
+            const uint64_t a = k * kUpPiece, b = std::min(bytes, a + kUpPiece);
+            char* stage = c.h_up + (uint64_t)slot * kUpPiece;
+            if (!err.load()) {
+                memcpy(stage, (const char*)src + a, b - a);
+                if (cudaMemcpyAsync((char*)dst + a, stage, b - a, cudaMemcpyHostToDevice, c.st) != cudaSuccess) err.store(1);
+            }
+            if (cudaEventRecord(c.up_ev[slot], c.st) != cudaSuccess) err.store(1);
+            c.up_done[slot].store(g + 1, std::memory_order_release);  // always, so that no later piece waits forever
+        }
+    };
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < nthreads; ++t) pool.emplace_back(work);
+    work();
+    for (auto& th : pool) th.join();
+    c.up_issued = base + npieces;
+    if (err.load()) return fail(VKM_ERR_CUDA, "staged host-to-device copy failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return VKM_OK;
+}
+
 int ctx_bind(HostCtx& c) {
     if (vkm_device_count() == 0) return fail(VKM_ERR_NO_DEVICE, "no CUDA device: vkmesh_b200 has no CPU path");
     const int dev = c.devices[0];
@@ -808,6 +897,7 @@ int ctx_bind(HostCtx& c) {
         c.scratch.release(); c.flag.release();
         for (auto e : c.chunk_ev) cudaEventDestroy(e);  // events belong to the device they were created on
         c.chunk_ev.clear();
+        release_upload_ring(c);
         if (c.st) cudaStreamDestroy(c.st);
         c.st = nullptr;
         CU(cudaStreamCreateWithFlags(&c.st, cudaStreamNonBlocking));
@@ -884,6 +974,7 @@ static void release_ctx(HostCtx& c) {
     c.h_stage_cap = 0;
     for (auto e : c.chunk_ev) cudaEventDestroy(e);
     c.chunk_ev.clear();
+    release_upload_ring(c);
     if (c.st) cudaStreamDestroy(c.st);
     c.st = nullptr;
     c.bound_device = -1;
@@ -1078,10 +1169,10 @@ static int lane_import(HostCtx& c, const float* pos, uint64_t np, const float* n
     if ((rc = c.idx.ensure(3 * C + 16))) return rc;
     {
         Gate g(c.h2d_gate);
-        if (np) CU(cudaMemcpyAsync(c.pos.p, pos, np * 12, cudaMemcpyHostToDevice, c.st));
-        if (nn) CU(cudaMemcpyAsync(c.nrm.p, nrm, nn * 12, cudaMemcpyHostToDevice, c.st));
-        if (nt) CU(cudaMemcpyAsync(c.uv.p, uv, nt * 8, cudaMemcpyHostToDevice, c.st));
-        if (C) CU(cudaMemcpyAsync(c.idx.p, idx, C * 12, cudaMemcpyHostToDevice, c.st));
+        if ((rc = upload_stream(c, c.pos.p, pos, np * 12))) return rc;
+        if ((rc = upload_stream(c, c.nrm.p, nrm, nn * 12))) return rc;
+        if ((rc = upload_stream(c, c.uv.p, uv, nt * 8))) return rc;
+        if ((rc = upload_stream(c, c.idx.p, idx, C * 12))) return rc;
         if (c.h2d_gate) CU(cudaStreamSynchronize(c.st));  // hold the direction until the upload has landed
     }
     tr.mark("enqueue H2D");
