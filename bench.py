@@ -151,7 +151,7 @@ def cpu_reference_run(n: int, repeats: int, threads: int = 1):
     return m.triangles * repeats * max(threads, 1) / dt, kind, m.triangles, dt
 
 
-def run_reference(args, rank, world):
+def run_reference(args, rank, world, emit):
     if rank != 0:
         return
     # The reference imports one mesh on one thread (MeshLoader::LoadOBJ has no parallel section), so the most host
@@ -178,7 +178,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------ our arm
@@ -206,8 +206,18 @@ def main():
                *sys.argv[1:]]
         sys.exit(subprocess.call(cmd))
 
+    # stdout carries exactly ONE line (the JSON): anything a library prints there (NCCL's version banner, ...) is sent
+    # to stderr by pointing fd 1 at fd 2 for the duration of the run; emit() writes the line to the real stdout.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line: dict) -> None:
+        sys.stdout.flush()
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
+
     if args.impl == "reference":
-        run_reference(args, rank, world)
+        run_reference(args, rank, world, emit)
         return
 
     import torch
@@ -493,7 +503,7 @@ def main():
             "roofline": roofline, "pipeline_roofline": pipeline_roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
             "gpu_launches": KERNELS_PER_STEP * args.steps, "clocks": clocks,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
