@@ -69,5 +69,5 @@ def assert_shapes_equal(got, want, tangent_ulp: int = 0):
         assert np.array_equal(g.indices, w.indices), f"shape {i}: index buffer differs at {np.argwhere(g.indices != w.indices)[:3].ravel()}"
         ok, msg = vertices_equal(g.vertices, w.vertices, tangent_ulp)
         assert ok, f"shape {i}: {msg}"
-        assert np.array_equal(np.asarray(g.extent, np.float32), np.asarray(w.extent, np.float32)), \
+        assert np.array_equal(np.asarray(g.extent, np.float32), np.asarray(w.extent, np.float32), equal_nan=True), \
             f"shape {i}: extent {g.extent} vs {w.extent}"

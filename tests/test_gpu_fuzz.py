@@ -1,0 +1,99 @@
+"""Seeded fuzz of the import path against the oracle (pytest -m gpu): small random meshes that mix everything the
+dedup contract distinguishes -- incoherent index order, few attribute records combined into many triplets, repeated
+attribute VALUES under different indices (value duplicates), +-0 twins, 1-ulp twins, NaN / Inf components, degenerate
+triangles, several shapes with empty ones in between -- through every host route (single call, batch lanes, both
+result memories, the device-resident plan).  Bit-exact, as in test_gpu_parity.py.
+"""
+import numpy as np
+import pytest
+from conftest import assert_shapes_equal
+
+from oracle import port
+from vulkanengine_b200 import capi, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def random_mesh(rng: np.random.Generator) -> synth.MeshStreams:
+    npos, nnrm, nuv = (int(rng.integers(1, hi)) for hi in rng.choice([4, 40, 400], 3))
+    pos = rng.standard_normal((npos, 3)).astype(np.float32)
+    nrm = rng.standard_normal((nnrm, 3)).astype(np.float32)
+    uv = rng.random((nuv, 2)).astype(np.float32)
+    for arr in (pos, nrm, uv):
+        n = len(arr)
+        k = int(rng.integers(0, max(1, n // 3) + 1))
+        for _ in range(k):  # injected special records
+            i, j = int(rng.integers(0, n)), int(rng.integers(0, n))
+            kind = int(rng.integers(0, 6))
+            if kind == 0:
+                arr[i] = arr[j]                                   # same values under another index
+            elif kind == 1:
+                arr[i] = arr[j]
+                arr[i, 0] = np.float32(0.0) * np.float32(-1.0)    # -0 ...
+                arr[j, 0] = np.float32(0.0)                       # ... and its +0 twin: must merge
+            elif kind == 2:
+                arr[i] = arr[j]
+                arr[i, 1] = np.nextafter(arr[j, 1], np.float32(np.inf))  # 1 ulp apart: must not merge
+            elif kind == 3:
+                arr[i, int(rng.integers(0, arr.shape[1]))] = np.float32(np.nan)
+            elif kind == 4:
+                arr[i, int(rng.integers(0, arr.shape[1]))] = np.float32(np.inf) * np.float32(rng.choice([-1.0, 1.0]))
+            else:
+                arr[i] = np.float32(0.0)
+    ntri = int(rng.integers(0, rng.choice([8, 200, 3000])))
+    idx = np.stack([rng.integers(0, npos, 3 * ntri), rng.integers(0, nnrm, 3 * ntri), rng.integers(0, nuv, 3 * ntri)], 1)
+    if ntri and rng.random() < 0.5:  # runs of repeated corners (degenerate triangles, heavy duplication)
+        rep = rng.integers(0, 3 * ntri, 3 * ntri // 2)
+        idx[rng.integers(0, 3 * ntri, len(rep))] = idx[rep]
+    idx = idx.astype(np.int32)
+    nshapes = int(rng.integers(1, 6))
+    cuts = np.sort(rng.integers(0, ntri + 1, nshapes - 1)) * 3
+    so = np.concatenate([[0], cuts, [3 * ntri]]).astype(np.uint64)
+    return synth.MeshStreams(pos, nrm, uv, idx, so)
+
+
+def oracle_of(m):
+    return port.import_arrays(m.pos, m.nrm, m.uv, m.idx, m.shape_offsets)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_fuzz_single_calls_match_oracle(seed):
+    rng = np.random.default_rng(0xF00D0000 + seed)
+    for k in range(40):
+        m = random_mesh(rng)
+        capi.set_result_memory(k & 1)
+        try:
+            got = capi.import_shapes(m.pos, m.nrm, m.uv, m.idx, m.shape_offsets)
+        finally:
+            capi.set_result_memory(0)
+        assert_shapes_equal(got, oracle_of(m))
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_fuzz_batch_lanes_match_oracle(mode):
+    rng = np.random.default_rng(0xBA7C4 + mode)
+    meshes = [random_mesh(rng) for _ in range(60)]
+    capi.set_result_memory(mode)
+    try:
+        got = capi.import_batch(meshes)
+    finally:
+        capi.set_result_memory(0)
+    for m, g in zip(meshes, got):
+        assert_shapes_equal(g, oracle_of(m))
+
+
+def test_fuzz_device_resident_plan_reused_across_clean_and_dirty_meshes():
+    """One plan, many imports: the short schedule is chosen from the previous import's outcome, so alternate clean
+    grids with dirty random meshes and check every result."""
+    rng = np.random.default_rng(0x9A7)
+    plan = capi.Plan(0, 20000, max_attrib=2000, max_vertices=20000, max_shapes=8)
+    for k in range(30):
+        m = synth.grid(int(rng.integers(2, 30))) if k % 3 == 0 else random_mesh(rng)
+        if m.corners == 0:
+            continue
+        d = [capi.DeviceArray(0, np.ascontiguousarray(a)) for a in (m.pos, m.nrm, m.uv, m.idx)]
+        plan.import_async(d[0].ptr, len(m.pos), d[1].ptr, len(m.nrm), d[2].ptr, len(m.uv), d[3].ptr, m.shape_offsets)
+        r = plan.finish()
+        assert_shapes_equal(plan.fetch(r, m.shape_offsets), oracle_of(m))
+        for x in d:
+            x.free()
