@@ -558,7 +558,7 @@ __global__ void __launch_bounds__(kThreads) k_flag_firsts(ImportArgs a) {
 // passes before it ran on the assumption "clean"; if the status block says otherwise, vkm_plan_finish re-runs
 // the import with the full schedule (k_resolve_slots first).
 template <bool DETECT>
-__global__ void __launch_bounds__(kThreads, 8) k_write_vertices(ImportArgs a) {
+__global__ void __launch_bounds__(kThreads, 6) k_write_vertices(ImportArgs a) {
     const uint32_t npairs = a.m1 >> 1;  // one thread per pair of slots, as in k_resolve_slots
     const bool fuse = import_is_clean(a);
     const bool fast = trip_is_fast(a);

@@ -357,8 +357,8 @@ int plan_enqueue(vkm_plan* p) {
     if (full) k_final_index<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
     k_write_indices<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_VERTICES], st));
-    if (full) k_write_vertices<false><<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
-    else k_write_vertices<true><<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
+    if (full) k_write_vertices<false><<<grid_for(a.m1 / 2, kThreads, dev, 6), kThreads, 0, st>>>(a);
+    else k_write_vertices<true><<<grid_for(a.m1 / 2, kThreads, dev, 6), kThreads, 0, st>>>(a);
     if (full) k_write_unmatchable_vertices<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
     if (T) CU(cudaEventRecord(ev[PH_TANGENTS], st));
     if (full)
