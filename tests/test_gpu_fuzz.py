@@ -97,3 +97,34 @@ def test_fuzz_device_resident_plan_reused_across_clean_and_dirty_meshes():
         assert_shapes_equal(plan.fetch(r, m.shape_offsets), oracle_of(m))
         for x in d:
             x.free()
+
+
+def test_no_device_or_host_memory_growth_over_many_calls():
+    """Soak: a few hundred host calls of varying size in both result modes must not grow device memory (NVML) or
+    the process' resident set beyond what the first rounds settle at."""
+    import os
+
+    import psutil
+    import pynvml
+
+    pynvml.nvmlInit()
+    h = pynvml.nvmlDeviceGetHandleByIndex(0)
+    proc = psutil.Process(os.getpid())
+    rng = np.random.default_rng(0x50A4)
+    meshes = [synth.grid(int(n)) for n in rng.integers(8, 200, 12)] + [random_mesh(rng) for _ in range(12)]
+
+    def round_():
+        for k, m in enumerate(meshes):
+            capi.set_result_memory(k & 1)
+            capi.import_shapes(m.pos, m.nrm, m.uv, m.idx, m.shape_offsets)
+        capi.set_result_memory(0)
+        capi.import_batch(meshes[:8])
+
+    for _ in range(3):
+        round_()
+    dev0, rss0 = pynvml.nvmlDeviceGetMemoryInfo(h).used, proc.memory_info().rss
+    for _ in range(12):
+        round_()
+    dev1, rss1 = pynvml.nvmlDeviceGetMemoryInfo(h).used, proc.memory_info().rss
+    assert dev1 - dev0 <= 64 << 20, f"device memory grew by {(dev1 - dev0) >> 20} MiB"
+    assert rss1 - rss0 <= 256 << 20, f"resident set grew by {(rss1 - rss0) >> 20} MiB"
