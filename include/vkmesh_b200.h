@@ -89,7 +89,12 @@ uint32_t vkm_deduplicate_vertices(uint32_t vertex_count, const void* vertices, u
  *   idx_vnt         : concatenated tinyobj::index_t streams, 3 ints per corner in (vertex, normal, texcoord)
  *                     order (tinyobj.hpp:347-351)
  *   shape_corner_offsets : nshapes + 1 offsets into idx_vnt, in corners (each a multiple of 3)
- *   out             : nshapes entries, filled with malloc()ed buffers; release with vkm_free_shape(). */
+ *   out             : nshapes entries, filled with malloc()ed buffers (or see vkm_set_result_memory); release
+ *                     with vkm_free_shape().
+ * The input arrays may be ordinary pageable memory (staged through the library's page-locked ring) or come from
+ * vkm_host_alloc() (copied directly).  Device scratch is cached between calls and sized from the inputs; when a
+ * mesh has more unique vertices than its attribute arrays suggest the import is repeated once with the exact
+ * size. */
 int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t nn, const float* uv, uint64_t nt,
                       const int32_t* idx_vnt, const uint64_t* shape_corner_offsets, uint32_t nshapes,
                       vkm_shape_out* out);
@@ -98,11 +103,13 @@ void vkm_free_shape(vkm_shape_out* shape);
 /* Where the host entry points (vkm_import_shapes, vkm_import_batch, vkm_import_obj_text) put their results.
  *   0 (default): malloc()ed buffers, one pair per shape -- what GeometryConfig owns in the reference
  *                (Platform::AllocMemory == malloc at mesh_loader.cpp:303-311, released with
- *                Platform::FrMemory == free at mesh_resource.cpp:13-18).  Costs one host copy out of the page-locked staging.
+ *                Platform::FrMemory == free at mesh_resource.cpp:13-18).  Costs one host copy out of the
+ *                page-locked staging.
  *   1          : page-locked blocks owned by the library and recycled: one block per call, the device writes
  *                the results into it directly (no staging copy, no page faults).  The buffers MUST then be
  *                released with vkm_free_shape(), never free(); idle blocks are kept for reuse up to
- *                VKM_RESULT_POOL_MAX_MB (environment; default a quarter of host memory, at least 8192) and dropped by vkm_shutdown() or mode 0.
+ *                VKM_RESULT_POOL_MAX_MB (environment; default a quarter of host memory, at least 8192) and dropped
+ *                by vkm_shutdown() or mode 0.
  * vkm_free_shape() accepts buffers of either kind, so the mode can change while results are outstanding.
  * No counterpart in the reference (its loader has no device). */
 int vkm_set_result_memory(int mode);
