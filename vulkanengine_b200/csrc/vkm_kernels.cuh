@@ -719,4 +719,48 @@ __global__ void __launch_bounds__(kThreads) k_per_vertex_frames(float4* vtx, con
     }
 }
 
+// The same result from the face side (stand-alone utilities): one thread per triangle reads its three indices
+// (coalesced, every sector used -- the per-vertex variant above gathers 12 bytes out of one or two 32-byte sectors
+// per vertex), asks for each corner whether this triangle is that vertex's last one, and only then evaluates the
+// frame once and writes it to the vertices it wins.  A triangle that repeats a vertex writes the same value twice.
+template <int MODE>
+__global__ void __launch_bounds__(kThreads) k_face_frames(float4* vtx, const uint32_t* __restrict__ indices,
+                                                          uint32_t index_count, const uint32_t* __restrict__ lastface,
+                                                          uint32_t vertex_limit) {
+    const uint32_t ntri = index_count / 3;
+    for (uint32_t f = blockIdx.x * blockDim.x + threadIdx.x; f < ntri; f += gridDim.x * blockDim.x) {
+        uint32_t i[3];
+        bool ok = true, wins[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            i[k] = __ldg(indices + 3ull * f + k);
+            ok &= (i[k] < vertex_limit);
+        }
+        if (!ok) continue;  // k_last_face has raised the flag; the reference would read out of bounds here
+        bool any = false;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            wins[k] = (__ldg(lastface + i[k]) == f + 1);
+            any |= wins[k];
+        }
+        if (!any) continue;
+        Tri t;
+        load_tri(vtx, i, t);
+        if (MODE == 0) {
+            const float4 tg = tangent_of(t);
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+                if (wins[k]) vtx[4ull * i[k] + 3] = tg;
+        } else {
+            const float3 n = normal_of(t);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                if (!wins[k]) continue;
+                float* dst = reinterpret_cast<float*>(vtx + 4ull * i[k]) + 3;
+                dst[0] = n.x; dst[1] = n.y; dst[2] = n.z;
+            }
+        }
+    }
+}
+
 }  // namespace vkm

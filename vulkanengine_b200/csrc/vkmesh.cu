@@ -606,11 +606,11 @@ static int frames_dev(int mode, uint32_t vertex_count, void* d_vertices, uint32_
     k_last_face<<<grid_for(index_count / 3, kThreads, dev), kThreads, 0, st>>>(d_indices, index_count, vertex_count,
                                                                              d_scratch, d_bad);
     if (mode == 0)
-        k_per_vertex_frames<0><<<grid_for(vertex_count, kThreads, dev), kThreads, 0, st>>>(
-            (float4*)d_vertices, d_indices, d_scratch, nullptr, vertex_count, nullptr, nullptr, 1, vertex_count, nullptr);
+        k_face_frames<0><<<grid_for(index_count / 3, kThreads, dev), kThreads, 0, st>>>((float4*)d_vertices, d_indices,
+                                                                                      index_count, d_scratch, vertex_count);
     else
-        k_per_vertex_frames<1><<<grid_for(vertex_count, kThreads, dev), kThreads, 0, st>>>(
-            (float4*)d_vertices, d_indices, d_scratch, nullptr, vertex_count, nullptr, nullptr, 1, vertex_count, nullptr);
+        k_face_frames<1><<<grid_for(index_count / 3, kThreads, dev), kThreads, 0, st>>>((float4*)d_vertices, d_indices,
+                                                                                      index_count, d_scratch, vertex_count);
     CU(cudaGetLastError());
     return VKM_OK;
 }
