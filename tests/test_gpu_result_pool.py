@@ -101,3 +101,39 @@ def test_empty_shapes_and_bad_mode(pooled):
     so = np.array([0, 0, len(m.idx), len(m.idx)], np.uint64)  # empty, whole mesh, empty
     got = capi.import_shapes(m.pos, m.nrm, m.uv, m.idx, so)
     assert_shapes_equal(got, port.import_arrays(m.pos, m.nrm, m.uv, m.idx, so))
+
+
+def test_batch_group_with_one_bad_mesh_reports_per_mesh_status():
+    """Small meshes of a batch are coalesced into one segmented import; a mesh with an out-of-range index must fail
+    alone (its index may not alias a neighbour's records) while the others import normally."""
+    L = capi.lib()
+    meshes = synth.batch(9, seed=3, min_tris=50, max_tris=400)
+    bad = 4
+    meshes[bad].idx = meshes[bad].idx.copy()
+    meshes[bad].idx[7, 1] = len(meshes[bad].nrm)  # one past the end of ITS normals, valid in the concatenation
+    n = len(meshes)
+    ins = (capi.MeshIn * n)()
+    outs = (C.POINTER(capi.ShapeOut) * n)()
+    keep = []
+    for i, m in enumerate(meshes):
+        so = np.ascontiguousarray(m.shape_offsets, np.uint64)
+        arr = (capi.ShapeOut * 1)()
+        keep += [so, arr]
+        ins[i] = capi.MeshIn(m.pos.ctypes.data, len(m.pos), m.nrm.ctypes.data, len(m.nrm), m.uv.ctypes.data, len(m.uv),
+                             m.idx.ctypes.data, so.ctypes.data, 1)
+        outs[i] = C.cast(arr, C.POINTER(capi.ShapeOut))
+    st = (C.c_int * n)()
+    rc = L.vkm_import_batch(ins, n, outs, st)
+    assert rc == 2  # VKM_ERR_BAD_INDEX
+    assert f"mesh {bad}" in L.vkm_last_error().decode()
+    for i, m in enumerate(meshes):
+        if i == bad:
+            assert st[i] != 0
+            continue
+        assert st[i] == 0
+        o = outs[i][0]
+        want = port.import_arrays(m.pos, m.nrm, m.uv, m.idx, m.shape_offsets)[0]
+        got_idx = np.frombuffer(C.string_at(o.indices, 4 * o.index_count), np.uint32)
+        assert np.array_equal(got_idx, want.indices)
+        assert o.vertex_count == len(want.vertices)
+        L.vkm_free_shape(C.byref(o))

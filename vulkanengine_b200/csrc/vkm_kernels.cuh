@@ -763,4 +763,37 @@ __global__ void __launch_bounds__(kThreads) k_face_frames(float4* vtx, const uin
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Batches of small meshes (vkm_import_batch): several meshes, each with attribute arrays of its own, are laid
+// end to end in one set of device arrays and imported as ONE multi-shape stream.  This kernel turns every
+// mesh's file-local indices into indices of the concatenated arrays (in the library's own device copy of the
+// stream) and checks them against that mesh's own record counts, so that a bad index cannot alias a neighbour.
+// ---------------------------------------------------------------------------------------------
+struct MeshSpan {
+    uint32_t c_begin, c_end;               // corner range of the mesh in the concatenated stream
+    uint32_t pos_base, nrm_base, uv_base;  // first record of the mesh in the concatenated attribute arrays
+    uint32_t np, nn, nt;                   // the mesh's own record counts
+};
+
+__global__ void __launch_bounds__(kThreads) k_rebase_indices(int32_t* idx, const MeshSpan* __restrict__ spans,
+                                                             uint32_t nmesh, uint32_t ncorners, uint32_t* bad) {
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < ncorners; c += gridDim.x * blockDim.x) {
+        uint32_t lo = 0, hi = nmesh;  // largest m with c_begin <= c (meshes without corners are skipped)
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (__ldg(&spans[mid].c_begin) <= c) lo = mid; else hi = mid;
+        }
+        const MeshSpan sp = spans[lo];
+        int32_t* o = idx + 3ull * c;
+        const uint32_t v = (uint32_t)o[0], n = (uint32_t)o[1], t = (uint32_t)o[2];
+        if (v >= sp.np || n >= sp.nn || t >= sp.nt) {  // negative ints are huge as unsigned
+            bad[lo] = 1;
+            continue;
+        }
+        o[0] = (int32_t)(v + sp.pos_base);
+        o[1] = (int32_t)(n + sp.nrm_base);
+        o[2] = (int32_t)(t + sp.uv_base);
+    }
+}
+
 }  // namespace vkm

@@ -715,7 +715,10 @@ struct HostCtx {
     static constexpr unsigned kUpSlots = 32;
     char* h_up = nullptr;
     std::vector<cudaEvent_t> up_ev;
-    uint64_t up_issued = 0;                    // pieces queued so far, over all calls (piece g uses slot g % kUpSlots)
+    // vkm_import_batch groups: per-mesh spans / bad-index flags of a coalesced group
+    DevBuf<MeshSpan> spans;
+    DevBuf<uint32_t> span_bad;
+    uint64_t up_issued = 0;                    // bins queued so far, over all calls (bin g uses slot g % kUpSlots)
     std::atomic<uint64_t> up_done[kUpSlots]{};  // per slot: 1 + the last piece whose DMA and event have been queued
 };
 constexpr uint64_t kUpPiece = HostCtx::kUpPiece;
@@ -825,21 +828,37 @@ bool is_page_locked(const void* p) {
     return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
 }
 
-// Host-to-device copy of one input stream.  Page-locked sources go straight to the copy engine.  Pageable sources
-// (what a drop-in caller has: tinyobj's vectors) would be bounced by the driver on one thread at a few GB/s; here a
-// few host threads copy 4 MiB pieces into a page-locked ring and queue each piece's DMA as soon as it is staged.
-// A ring slot is reused once the DMA that last read it has completed (per-slot event + sequence number).
-int upload_stream(HostCtx& c, void* dst, const void* src, uint64_t bytes) {
-    if (bytes == 0) return VKM_OK;
-    if (bytes < 2 * kUpPiece || is_page_locked(src)) {
-        CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.st));
-        return VKM_OK;
+// Host-to-device copies of a list of input arrays.  Page-locked sources go straight to the copy engine.  Pageable
+// sources (what a drop-in caller has: tinyobj's vectors) would be bounced by the driver on the calling thread at a
+// few GB/s; here they are cut into pieces of at most 4 MiB, the pieces are packed into 4 MiB bins, and a few host
+// threads copy one bin each into a slot of a page-locked ring and queue its DMAs as soon as it is staged (so many
+// small arrays cost one staging pass, not one blocking driver copy each).  A ring slot is reused once the DMAs that
+// last read it have completed (per-slot event + sequence number, carried across calls).
+struct UpSeg {
+    char* dst;
+    const char* src;
+    uint64_t bytes;
+};
+
+int upload_segments(HostCtx& c, const std::vector<UpSeg>& segs) {
+    std::vector<UpSeg> pieces;  // pageable, <= kUpPiece each
+    uint64_t staged_bytes = 0;
+    for (const UpSeg& sg : segs) {
+        if (sg.bytes == 0) continue;
+        if (is_page_locked(sg.src)) {
+            CU(cudaMemcpyAsync(sg.dst, sg.src, sg.bytes, cudaMemcpyHostToDevice, c.st));
+            continue;
+        }
+        for (uint64_t a = 0; a < sg.bytes; a += kUpPiece)
+            pieces.push_back(UpSeg{sg.dst + a, sg.src + a, std::min(kUpPiece, sg.bytes - a)});
+        staged_bytes += sg.bytes;
     }
+    if (pieces.empty()) return VKM_OK;
     if (!c.h_up) {
         if (cudaMallocHost((void**)&c.h_up, kUpPiece * kUpSlots) != cudaSuccess) {
             cudaGetLastError();
-            c.h_up = nullptr;
-            CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.st));  // no page-locked memory: plain copy
+            c.h_up = nullptr;  // no page-locked memory to be had: plain copies
+            for (const UpSeg& pc : pieces) CU(cudaMemcpyAsync(pc.dst, pc.src, pc.bytes, cudaMemcpyHostToDevice, c.st));
             return VKM_OK;
         }
         for (unsigned i = 0; i < kUpSlots; ++i) {
@@ -848,9 +867,27 @@ int upload_stream(HostCtx& c, void* dst, const void* src, uint64_t bytes) {
             c.up_ev.push_back(e);
         }
     }
-    const uint64_t npieces = (bytes + kUpPiece - 1) / kUpPiece;
+    // bins: runs of consecutive pieces that fit one slot (device offsets inside a slot stay 256-byte aligned)
+    std::vector<std::pair<uint32_t, uint32_t>> bins;
+    {
+        uint64_t fill = 0;
+        uint32_t first = 0;
+        for (uint32_t i = 0; i < pieces.size(); ++i) {
+            const uint64_t need = (pieces[i].bytes + 255) & ~255ull;
+            if (fill + need > kUpPiece && i > first) {
+                bins.push_back({first, i});
+                first = i;
+                fill = 0;
+            }
+            fill += need;
+        }
+        bins.push_back({first, (uint32_t)pieces.size()});
+    }
+    const uint64_t nbins = bins.size();
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-    const unsigned nthreads = (unsigned)std::min<uint64_t>(std::min(std::max(1u, c.copy_threads), hw), npieces);
+    // small uploads are not worth waking threads for
+    const uint64_t by_size = std::max<uint64_t>(1, staged_bytes / (2 * kUpPiece));
+    const unsigned nthreads = (unsigned)std::min<uint64_t>(std::min<uint64_t>(std::min(std::max(1u, c.copy_threads), hw), nbins), by_size);
     std::atomic<uint64_t> next{0};
     std::atomic<int> err{0};
     const uint64_t base = c.up_issued;
@@ -859,30 +896,32 @@ int upload_stream(HostCtx& c, void* dst, const void* src, uint64_t bytes) {
         cudaSetDevice(dev);
         for (;;) {
             const uint64_t k = next.fetch_add(1);
-            if (k >= npieces) return;
+            if (k >= nbins) return;
             const uint64_t g = base + k;
             const unsigned slot = (unsigned)(g % kUpSlots);
             if (g >= kUpSlots) {
-                // the slot's previous user (piece g - kUpSlots, possibly of an earlier call) has queued its DMA ...
+                // the slot's previous user (bin g - kUpSlots, possibly of an earlier call) has queued its DMAs ...
                 while (c.up_done[slot].load(std::memory_order_acquire) < g - kUpSlots + 1) std::this_thread::yield();
-                // ... and that DMA has finished reading the slot
+                // ... and they have finished reading the slot
                 if (cudaEventSynchronize(c.up_ev[slot]) != cudaSuccess) err.store(1);
             }
-            const uint64_t a = k * kUpPiece, b = std::min(bytes, a + kUpPiece);
             char* stage = c.h_up + (uint64_t)slot * kUpPiece;
-            if (!err.load()) {
-                memcpy(stage, (const char*)src + a, b - a);
-                if (cudaMemcpyAsync((char*)dst + a, stage, b - a, cudaMemcpyHostToDevice, c.st) != cudaSuccess) err.store(1);
+            uint64_t off = 0;
+            for (uint32_t i = bins[k].first; i < bins[k].second && !err.load(); ++i) {
+                const UpSeg& pc = pieces[i];
+                memcpy(stage + off, pc.src, pc.bytes);
+                if (cudaMemcpyAsync(pc.dst, stage + off, pc.bytes, cudaMemcpyHostToDevice, c.st) != cudaSuccess) err.store(1);
+                off += (pc.bytes + 255) & ~255ull;
             }
             if (cudaEventRecord(c.up_ev[slot], c.st) != cudaSuccess) err.store(1);
-            c.up_done[slot].store(g + 1, std::memory_order_release);  // always, so that no later piece waits forever
+            c.up_done[slot].store(g + 1, std::memory_order_release);  // always, so that no later bin waits forever
         }
     };
     std::vector<std::thread> pool;
     for (unsigned t = 1; t < nthreads; ++t) pool.emplace_back(work);
     work();
     for (auto& th : pool) th.join();
-    c.up_issued = base + npieces;
+    c.up_issued = base + nbins;
     if (err.load()) return fail(VKM_ERR_CUDA, "staged host-to-device copy failed: %s", cudaGetErrorString(cudaGetLastError()));
     return VKM_OK;
 }
@@ -894,7 +933,7 @@ int ctx_bind(HostCtx& c) {
     if (c.bound_device != dev) {
         if (c.plan) { vkm_plan_destroy(c.plan); c.plan = nullptr; }
         c.pos.release(); c.nrm.release(); c.uv.release(); c.idx.release(); c.vtx.release(); c.ind.release();
-        c.scratch.release(); c.flag.release();
+        c.scratch.release(); c.flag.release(); c.spans.release(); c.span_bad.release();
         for (auto e : c.chunk_ev) cudaEventDestroy(e);  // events belong to the device they were created on
         c.chunk_ev.clear();
         release_upload_ring(c);
@@ -968,7 +1007,7 @@ static void release_ctx(HostCtx& c) {
     cudaSetDevice(c.bound_device);
     if (c.plan) { vkm_plan_destroy(c.plan); c.plan = nullptr; }
     c.pos.release(); c.nrm.release(); c.uv.release(); c.idx.release(); c.vtx.release(); c.ind.release();
-    c.scratch.release(); c.flag.release();
+    c.scratch.release(); c.flag.release(); c.spans.release(); c.span_bad.release();
     if (c.h_stage) cudaFreeHost(c.h_stage);
     c.h_stage = nullptr;
     c.h_stage_cap = 0;
@@ -1169,14 +1208,87 @@ static int lane_import(HostCtx& c, const float* pos, uint64_t np, const float* n
     if ((rc = c.idx.ensure(3 * C + 16))) return rc;
     {
         Gate g(c.h2d_gate);
-        if ((rc = upload_stream(c, c.pos.p, pos, np * 12))) return rc;
-        if ((rc = upload_stream(c, c.nrm.p, nrm, nn * 12))) return rc;
-        if ((rc = upload_stream(c, c.uv.p, uv, nt * 8))) return rc;
-        if ((rc = upload_stream(c, c.idx.p, idx, C * 12))) return rc;
+        const std::vector<UpSeg> segs{{(char*)c.pos.p, (const char*)pos, np * 12}, {(char*)c.nrm.p, (const char*)nrm, nn * 12},
+                                      {(char*)c.uv.p, (const char*)uv, nt * 8}, {(char*)c.idx.p, (const char*)idx, C * 12}};
+        if ((rc = upload_segments(c, segs))) return rc;
         if (c.h2d_gate) CU(cudaStreamSynchronize(c.st));  // hold the direction until the upload has landed
     }
     tr.mark("enqueue H2D");
     return import_resident(c, c.pos.p, np, c.nrm.p, nn, c.uv.p, nt, c.idx.p, shape_off, nshapes, out, tr);
+}
+
+// Several small meshes as ONE import (vkm_import_batch): their arrays are laid end to end in the lane's device
+// buffers, k_rebase_indices makes the indices global (and checks them per mesh), and the import runs once over
+// all their shapes -- per-mesh launch, synchronisation and allocation costs are paid once per group.  Returns
+// VKM_OK with every member's shapes filled, or a non-zero code WITHOUT touching any output: the caller then imports
+// the members one by one, which also yields the per-mesh statuses and messages.
+static int lane_import_group(HostCtx& c, const vkm_mesh_in* meshes, const uint32_t* ids, uint32_t n,
+                             vkm_shape_out* const* outs) {
+    uint64_t NP = 0, NN = 0, NT = 0, C = 0, S = 0;
+    std::vector<MeshSpan> spans(n);
+    for (uint32_t k = 0; k < n; ++k) {
+        const vkm_mesh_in& m = meshes[ids[k]];
+        if (m.nshapes == 0 || !m.shape_corner_offsets || !outs[ids[k]] || m.shape_corner_offsets[0] != 0)
+            return VKM_ERR_INVALID_ARG;
+        const uint64_t mc = m.shape_corner_offsets[m.nshapes];
+        if (mc > 0 && (!m.pos || !m.nrm || !m.uv || !m.idx_vnt)) return VKM_ERR_INVALID_ARG;
+        for (uint32_t s = 0; s < m.nshapes; ++s) {
+            const uint64_t a = m.shape_corner_offsets[s], b = m.shape_corner_offsets[s + 1];
+            if (b < a || (b - a) % 3 != 0) return VKM_ERR_INVALID_ARG;
+        }
+        spans[k] = MeshSpan{(uint32_t)C, (uint32_t)(C + mc), (uint32_t)NP, (uint32_t)NN, (uint32_t)NT,
+                            (uint32_t)m.np, (uint32_t)m.nn, (uint32_t)m.nt};
+        NP += m.np; NN += m.nn; NT += m.nt; C += mc; S += m.nshapes;
+    }
+    if (C == 0 || NP == 0 || NN == 0 || NT == 0 || C > 0x7FFFFFF0ull || NP >= 0x7FFFFFFFull || NN >= 0x7FFFFFFFull ||
+        NT >= 0x7FFFFFFFull)
+        return VKM_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(c.mu);
+    Trace tr;
+    int rc = ctx_bind(c);
+    if (rc) return rc;
+    if ((rc = c.pos.ensure(3 * NP + 4)) || (rc = c.nrm.ensure(3 * NN + 4)) || (rc = c.uv.ensure(2 * NT + 4)) ||
+        (rc = c.idx.ensure(3 * C + 16)) || (rc = c.spans.ensure(n)) || (rc = c.span_bad.ensure(n)))
+        return rc;
+    std::vector<uint64_t> shape_off;
+    shape_off.reserve(S + 1);
+    shape_off.push_back(0);
+    std::vector<uint32_t> bad(n, 0);
+    {
+        Gate g(c.h2d_gate);
+        std::vector<UpSeg> segs;
+        segs.reserve(4ull * n);
+        for (uint32_t k = 0; k < n; ++k) {
+            const vkm_mesh_in& m = meshes[ids[k]];
+            const MeshSpan& sp = spans[k];
+            segs.push_back(UpSeg{(char*)(c.pos.p + 3ull * sp.pos_base), (const char*)m.pos, m.np * 12});
+            segs.push_back(UpSeg{(char*)(c.nrm.p + 3ull * sp.nrm_base), (const char*)m.nrm, m.nn * 12});
+            segs.push_back(UpSeg{(char*)(c.uv.p + 2ull * sp.uv_base), (const char*)m.uv, m.nt * 8});
+            segs.push_back(UpSeg{(char*)(c.idx.p + 3ull * sp.c_begin), (const char*)m.idx_vnt, (uint64_t)(sp.c_end - sp.c_begin) * 12});
+            for (uint32_t s = 1; s <= m.nshapes; ++s) shape_off.push_back(sp.c_begin + m.shape_corner_offsets[s]);
+        }
+        if ((rc = upload_segments(c, segs))) return rc;
+        CU(cudaMemcpyAsync(c.spans.p, spans.data(), n * sizeof(MeshSpan), cudaMemcpyHostToDevice, c.st));
+        CU(cudaMemsetAsync(c.span_bad.p, 0, (uint64_t)n * 4, c.st));
+        k_rebase_indices<<<grid_for(C, kThreads, c.bound_device), kThreads, 0, c.st>>>(c.idx.p, c.spans.p, n, (uint32_t)C,
+                                                                                        c.span_bad.p);
+        CU(cudaGetLastError());
+        CU(cudaMemcpyAsync(bad.data(), c.span_bad.p, (uint64_t)n * 4, cudaMemcpyDeviceToHost, c.st));
+        CU(cudaStreamSynchronize(c.st));  // spans / bad live on this stack frame; the uploads have landed
+    }
+    tr.mark("group upload + rebase");
+    for (uint32_t k = 0; k < n; ++k)
+        if (bad[k]) return VKM_ERR_BAD_INDEX;  // the one-by-one path names the mesh
+    std::vector<vkm_shape_out> flat(S);
+    init_shape_outs(flat.data(), (uint32_t)S);
+    if ((rc = import_resident(c, c.pos.p, NP, c.nrm.p, NN, c.uv.p, NT, c.idx.p, shape_off.data(), (uint32_t)S, flat.data(), tr)))
+        return rc;
+    uint64_t at = 0;
+    for (uint32_t k = 0; k < n; ++k) {
+        const vkm_mesh_in& m = meshes[ids[k]];
+        for (uint32_t s = 0; s < m.nshapes; ++s) outs[ids[k]][s] = flat[at++];
+    }
+    return VKM_OK;
 }
 
 int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t nn, const float* uv, uint64_t nt,
@@ -1188,7 +1300,8 @@ int vkm_import_shapes(const float* pos, uint64_t np, const float* nrm, uint64_t 
 // Batches of independent meshes over every selected GPU: the natural shard.
 // Meshes are partitioned over the devices of vkm_init() by longest-processing-time (corner count); every device
 // runs TWO lanes (own stream, plan, device inputs, pinned staging, host thread), so the host->device copy of one
-// mesh overlaps the kernels and the device->host copy of another (the copy engines are full duplex).  No
+// mesh overlaps the kernels and the device->host copy of another (the copy engines are full duplex).  Small
+// meshes are coalesced into groups that run as one segmented (multi-shape) import each, see lane_import_group.  No
 // inter-GPU traffic: results land in the caller's per-mesh output arrays.
 // ------------------------------------------------------------------------------------------------
 int vkm_import_batch(const vkm_mesh_in* meshes, uint32_t count, vkm_shape_out* const* outs, int* statuses) {
@@ -1226,6 +1339,31 @@ int vkm_import_batch(const vkm_mesh_in* meshes, uint32_t count, vkm_shape_out* c
         queue[best].push_back(i);
         load[best] += size_of(i);
     }
+    // Work units per device: a large mesh is a unit of its own; small meshes (below kSoloCorners) are coalesced, in
+    // queue order, into groups of up to kGroupCorners corners / kGroupMeshes meshes that run as one import each.
+    constexpr uint64_t kSoloCorners = 1ull << 20, kGroupCorners = 6ull << 20;
+    constexpr size_t kGroupMeshes = 1024;
+    std::vector<std::vector<std::vector<uint32_t>>> units(nd);
+    for (size_t d = 0; d < nd; ++d) {
+        std::vector<uint32_t> group;
+        uint64_t group_corners = 0;
+        auto flush = [&]() {
+            if (!group.empty()) units[d].push_back(group);
+            group.clear();
+            group_corners = 0;
+        };
+        for (uint32_t i : queue[d]) {
+            const uint64_t sz = size_of(i);
+            if (sz >= kSoloCorners || sz == 0) {  // (empty meshes keep the one-by-one path's early outs)
+                units[d].push_back({i});
+                continue;
+            }
+            if (group_corners + sz > kGroupCorners || group.size() >= kGroupMeshes) flush();
+            group.push_back(i);
+            group_corners += sz;
+        }
+        flush();
+    }
     std::vector<int> st(count, VKM_OK);
     std::vector<std::string> msgs(count);
     std::vector<std::atomic<uint32_t>> next(nd);
@@ -1234,12 +1372,16 @@ int vkm_import_batch(const vkm_mesh_in* meshes, uint32_t count, vkm_shape_out* c
         const size_t d = lane / 2;
         for (;;) {
             const uint32_t k = next[d].fetch_add(1);
-            if (k >= queue[d].size()) return;
-            const uint32_t i = queue[d][k];
-            const vkm_mesh_in& m = meshes[i];
-            st[i] = lane_import(*g_lanes[lane], m.pos, m.np, m.nrm, m.nn, m.uv, m.nt, m.idx_vnt, m.shape_corner_offsets,
-                                m.nshapes, outs[i]);
-            if (st[i] != VKM_OK) msgs[i] = g_err;  // thread-local message of this worker
+            if (k >= units[d].size()) return;
+            const std::vector<uint32_t>& unit = units[d][k];
+            if (unit.size() > 1 && lane_import_group(*g_lanes[lane], meshes, unit.data(), (uint32_t)unit.size(), outs) == VKM_OK)
+                continue;
+            for (uint32_t i : unit) {  // a single mesh, or a group that has to be taken apart
+                const vkm_mesh_in& m = meshes[i];
+                st[i] = lane_import(*g_lanes[lane], m.pos, m.np, m.nrm, m.nn, m.uv, m.nt, m.idx_vnt, m.shape_corner_offsets,
+                                    m.nshapes, outs[i]);
+                if (st[i] != VKM_OK) msgs[i] = g_err;  // thread-local message of this worker
+            }
         }
     };
     std::vector<std::thread> pool;
