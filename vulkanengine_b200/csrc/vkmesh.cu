@@ -845,7 +845,8 @@ int upload_segments(HostCtx& c, const std::vector<UpSeg>& segs) {
     uint64_t staged_bytes = 0;
     for (const UpSeg& sg : segs) {
         if (sg.bytes == 0) continue;
-        if (is_page_locked(sg.src)) {
+        // (the driver query costs microseconds: small arrays are staged whatever memory they are in)
+        if (sg.bytes >= (1ull << 20) && is_page_locked(sg.src)) {
             CU(cudaMemcpyAsync(sg.dst, sg.src, sg.bytes, cudaMemcpyHostToDevice, c.st));
             continue;
         }
@@ -867,19 +868,22 @@ int upload_segments(HostCtx& c, const std::vector<UpSeg>& segs) {
             c.up_ev.push_back(e);
         }
     }
-    // bins: runs of consecutive pieces that fit one slot (device offsets inside a slot stay 256-byte aligned)
+    // bins: runs of consecutive pieces that fit one slot.  A piece whose destination continues the previous one's
+    // (the arrays of a group's meshes are laid end to end on the device) is staged right behind it and shares its
+    // DMA; any other piece starts on a 256-byte boundary of the slot.
+    auto continues = [&](uint32_t i) { return i > 0 && pieces[i].dst == pieces[i - 1].dst + pieces[i - 1].bytes; };
     std::vector<std::pair<uint32_t, uint32_t>> bins;
     {
         uint64_t fill = 0;
         uint32_t first = 0;
         for (uint32_t i = 0; i < pieces.size(); ++i) {
-            const uint64_t need = (pieces[i].bytes + 255) & ~255ull;
-            if (fill + need > kUpPiece && i > first) {
+            uint64_t start = (i > first && continues(i)) ? fill : ((fill + 255) & ~255ull);
+            if (start + pieces[i].bytes > kUpPiece && i > first) {
                 bins.push_back({first, i});
                 first = i;
-                fill = 0;
+                start = 0;
             }
-            fill += need;
+            fill = start + pieces[i].bytes;
         }
         bins.push_back({first, (uint32_t)pieces.size()});
     }
@@ -907,11 +911,16 @@ int upload_segments(HostCtx& c, const std::vector<UpSeg>& segs) {
             }
             char* stage = c.h_up + (uint64_t)slot * kUpPiece;
             uint64_t off = 0;
-            for (uint32_t i = bins[k].first; i < bins[k].second && !err.load(); ++i) {
-                const UpSeg& pc = pieces[i];
-                memcpy(stage + off, pc.src, pc.bytes);
-                if (cudaMemcpyAsync(pc.dst, stage + off, pc.bytes, cudaMemcpyHostToDevice, c.st) != cudaSuccess) err.store(1);
-                off += (pc.bytes + 255) & ~255ull;
+            for (uint32_t i = bins[k].first; i < bins[k].second && !err.load();) {
+                off = (off + 255) & ~255ull;
+                const uint64_t run_at = off;
+                char* run_dst = pieces[i].dst;
+                do {  // a run of pieces with one contiguous destination: one DMA
+                    memcpy(stage + off, pieces[i].src, pieces[i].bytes);
+                    off += pieces[i].bytes;
+                    ++i;
+                } while (i < bins[k].second && continues(i));
+                if (cudaMemcpyAsync(run_dst, stage + run_at, off - run_at, cudaMemcpyHostToDevice, c.st) != cudaSuccess) err.store(1);
             }
             if (cudaEventRecord(c.up_ev[slot], c.st) != cudaSuccess) err.store(1);
             c.up_done[slot].store(g + 1, std::memory_order_release);  // always, so that no later bin waits forever
@@ -1101,15 +1110,23 @@ static int import_resident(HostCtx& c, const float* d_pos, uint64_t np, const fl
     const uint64_t C = shape_off[nshapes];
     const uint64_t max_attrib = std::max(np, std::max(nn, nt));
     if (!c.plan || c.plan->desc.max_corners < C || c.plan->desc.max_shapes < nshapes || c.plan->desc.max_attrib < max_attrib) {
-        if (c.plan) vkm_plan_destroy(c.plan);
-        c.plan = nullptr;
         vkm_plan_desc d{};
         d.device = c.devices[0];
         d.max_corners = C;
-        // unique vertices are usually close to the largest attribute array; the plan grows when they are not
-        d.max_vertices = std::min<uint64_t>(C, max_attrib + max_attrib / 8 + 1024);
         d.max_attrib = max_attrib;
         d.max_shapes = nshapes;
+        if (c.plan) {
+            // a caller with inputs of varying size (a batch): never shrink, and leave headroom, so that the plan is
+            // rebuilt a few times at most instead of once per call
+            const vkm_plan_desc& o = c.plan->desc;
+            d.max_corners = std::min<uint64_t>(kMaxCorners, std::max<uint64_t>(C + C / 4, o.max_corners));
+            d.max_attrib = std::max<uint64_t>(max_attrib + max_attrib / 4, o.max_attrib);
+            d.max_shapes = std::max<uint32_t>(nshapes < 0x7FFFFFFFu ? 2 * nshapes : nshapes, o.max_shapes);
+            vkm_plan_destroy(c.plan);
+        }
+        c.plan = nullptr;
+        // unique vertices are usually close to the largest attribute array; the plan grows when they are not
+        d.max_vertices = std::min<uint64_t>(d.max_corners, d.max_attrib + d.max_attrib / 8 + 1024);
         if ((rc = vkm_plan_create(&d, &c.plan))) return rc;
         c.plan->grow_vertices = true;
     }
@@ -1258,14 +1275,19 @@ static int lane_import_group(HostCtx& c, const vkm_mesh_in* meshes, const uint32
         Gate g(c.h2d_gate);
         std::vector<UpSeg> segs;
         segs.reserve(4ull * n);
+        // array kind by array kind: consecutive meshes then have consecutive destinations and share DMAs
+        for (int kind = 0; kind < 4; ++kind)
+            for (uint32_t k = 0; k < n; ++k) {
+                const vkm_mesh_in& m = meshes[ids[k]];
+                const MeshSpan& sp = spans[k];
+                if (kind == 0) segs.push_back(UpSeg{(char*)(c.pos.p + 3ull * sp.pos_base), (const char*)m.pos, m.np * 12});
+                if (kind == 1) segs.push_back(UpSeg{(char*)(c.nrm.p + 3ull * sp.nrm_base), (const char*)m.nrm, m.nn * 12});
+                if (kind == 2) segs.push_back(UpSeg{(char*)(c.uv.p + 2ull * sp.uv_base), (const char*)m.uv, m.nt * 8});
+                if (kind == 3) segs.push_back(UpSeg{(char*)(c.idx.p + 3ull * sp.c_begin), (const char*)m.idx_vnt, (uint64_t)(sp.c_end - sp.c_begin) * 12});
+            }
         for (uint32_t k = 0; k < n; ++k) {
             const vkm_mesh_in& m = meshes[ids[k]];
-            const MeshSpan& sp = spans[k];
-            segs.push_back(UpSeg{(char*)(c.pos.p + 3ull * sp.pos_base), (const char*)m.pos, m.np * 12});
-            segs.push_back(UpSeg{(char*)(c.nrm.p + 3ull * sp.nrm_base), (const char*)m.nrm, m.nn * 12});
-            segs.push_back(UpSeg{(char*)(c.uv.p + 2ull * sp.uv_base), (const char*)m.uv, m.nt * 8});
-            segs.push_back(UpSeg{(char*)(c.idx.p + 3ull * sp.c_begin), (const char*)m.idx_vnt, (uint64_t)(sp.c_end - sp.c_begin) * 12});
-            for (uint32_t s = 1; s <= m.nshapes; ++s) shape_off.push_back(sp.c_begin + m.shape_corner_offsets[s]);
+            for (uint32_t s = 1; s <= m.nshapes; ++s) shape_off.push_back(spans[k].c_begin + m.shape_corner_offsets[s]);
         }
         if ((rc = upload_segments(c, segs))) return rc;
         CU(cudaMemcpyAsync(c.spans.p, spans.data(), n * sizeof(MeshSpan), cudaMemcpyHostToDevice, c.st));
