@@ -118,7 +118,9 @@ int vkm_set_result_memory(int mode);
  * vkm_init(): the multi-GPU form of the same reference loop (each mesh is an independent dedup domain,
  * mesh_loader.cpp:322-324 clears all state between shapes; the reference itself has no multi-mesh entry).  Meshes
  * are partitioned over the devices by size (longest first); each device runs two lanes so that one mesh's copies
- * overlap another's kernels.  outs[i] must hold meshes[i].nshapes entries; statuses (optional) gets one code per
+ * overlap another's kernels.  Small meshes are grouped: a group's arrays are laid end to end on the device and run
+ * as one segmented import (every mesh's indices are checked against its own record counts first), so thousands of
+ * small assets do not pay thousands of launches and synchronisations; results and statuses stay per mesh.  outs[i] must hold meshes[i].nshapes entries; statuses (optional) gets one code per
  * mesh.  Returns the first failure's code, VKM_OK if every mesh imported. */
 typedef struct vkm_mesh_in {
     const float* pos;  uint64_t np;
