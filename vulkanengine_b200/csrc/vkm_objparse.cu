@@ -36,6 +36,7 @@
 #include <vector>
 
 extern "C" void vkm_internal_set_error(const char* msg);  // vkmesh.cu: feeds vkm_last_error()
+extern "C" void vkm_internal_parallel_run(unsigned n, void (*fn)(void*, unsigned), void* ctx);  // vkmesh.cu: helper pool
 extern "C" int vkm_internal_import_device(int device, const float* d_pos, uint64_t np, const float* d_nrm, uint64_t nn,
                                           const float* d_uv, uint64_t nt, const int32_t* d_idx, const uint64_t* shape_off,
                                           uint32_t nshapes, vkm_shape_out* out);
@@ -589,10 +590,8 @@ cudaError_t upload_text(ParseCtx& c, char* d_text, const char* text, uint64_t le
                 if (e != cudaSuccess) err.store((int)e);
             }
         };
-        std::vector<std::thread> pool;
-        for (unsigned t = 1; t < nthreads; ++t) pool.emplace_back(work);
-        work();
-        for (auto& th : pool) th.join();
+        vkm_internal_parallel_run(
+            nthreads, [](void* w, unsigned) { (*static_cast<decltype(work)*>(w))(); }, &work);
         if (err.load() != (int)cudaSuccess) return (cudaError_t)err.load();
         if (w0 + window < len) {  // the staging is reused by the next window
             const cudaError_t e = cudaStreamSynchronize(c.st);

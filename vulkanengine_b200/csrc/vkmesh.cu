@@ -10,10 +10,13 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <deque>
+#include <functional>
 #include <map>
 #include <mutex>
 #include <string>
@@ -164,6 +167,84 @@ struct ResultPool {
 };
 ResultPool g_results;
 std::atomic<int> g_result_mode{0};  // 0: malloc()ed results, 1: pooled page-locked results
+
+// Persistent helper threads for the host-side staging copies.  Starting and joining std::threads costs tens of
+// microseconds apiece, more than the copy itself for a mesh of a few megabytes; these helpers sleep on a condition
+// variable between jobs.  run(n, fn) executes fn(0) .. fn(n-1), index 0 on the caller; the caller also takes over any
+// index no helper has picked up yet, so a job completes even when every helper is busy with another lane's job.
+// The pool is created on first use and never destroyed (its threads are detached and idle at process exit).
+class HelperPool {
+public:
+    static HelperPool& get() {
+        static HelperPool* p = new HelperPool();
+        return *p;
+    }
+    void run(unsigned n, const std::function<void(unsigned)>& fn) {
+        if (n <= 1) {
+            fn(0);
+            return;
+        }
+        Job job{&fn, 1, n, {n - 1}};
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            const unsigned want = std::min(kMaxHelpers, n - 1);
+            while (workers_ < want) {
+                std::thread(&HelperPool::worker, this).detach();
+                ++workers_;
+            }
+            jobs_.push_back(&job);
+        }
+        cv_.notify_all();
+        fn(0);
+        for (;;) {  // help with what is left, then wait for the indices that helpers are running
+            unsigned idx;
+            {
+                std::lock_guard<std::mutex> lk(mu_);
+                if (!claim(&job, idx)) break;
+            }
+            fn(idx);
+            job.left.fetch_sub(1, std::memory_order_release);
+        }
+        while (job.left.load(std::memory_order_acquire) != 0) std::this_thread::yield();
+    }
+
+private:
+    struct Job {
+        const std::function<void(unsigned)>* fn;
+        unsigned next, n;           // next unclaimed index (under mu_)
+        std::atomic<unsigned> left;  // indices 1 .. n-1 not finished yet
+    };
+    static constexpr unsigned kMaxHelpers = 15;
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::deque<Job*> jobs_;  // jobs with unclaimed indices
+    unsigned workers_ = 0;
+
+    // under mu_: take the next index of `job` if it is still queued; drops the job from the queue with its last index
+    bool claim(Job* job, unsigned& idx) {
+        for (auto it = jobs_.begin(); it != jobs_.end(); ++it) {
+            if (*it != job) continue;
+            idx = job->next++;
+            if (job->next >= job->n) jobs_.erase(it);
+            return true;
+        }
+        return false;
+    }
+    void worker() {
+        for (;;) {
+            Job* job;
+            unsigned idx;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                cv_.wait(lk, [&] { return !jobs_.empty(); });
+                job = jobs_.front();
+                if (!claim(job, idx)) continue;
+            }
+            (*job->fn)(idx);
+            job->left.fetch_sub(1, std::memory_order_release);  // the job may be gone right after this
+        }
+    }
+};
 
 int sm_count(int device) {
     static int cached[64] = {0};
@@ -801,10 +882,7 @@ int download_staged(HostCtx& c, const void* d_vertices, uint64_t vbytes, const v
             copy_stage_range(c.h_stage, segs, k * kChunk, std::min(total, (k + 1) * kChunk));
         }
     };
-    std::vector<std::thread> pool;
-    for (unsigned t = 1; t < nthreads; ++t) pool.emplace_back(work, t);
-    work(0);
-    for (auto& th : pool) th.join();
+    HelperPool::get().run(nthreads, work);
     for (int e : errs)
         if (e) return fail(VKM_ERR_CUDA, "device-to-host copy failed: %s", cudaGetErrorString(cudaGetLastError()));
     return VKM_OK;
@@ -872,13 +950,14 @@ int upload_segments(HostCtx& c, const std::vector<UpSeg>& segs) {
     // (the arrays of a group's meshes are laid end to end on the device) is staged right behind it and shares its
     // DMA; any other piece starts on a 256-byte boundary of the slot.
     auto continues = [&](uint32_t i) { return i > 0 && pieces[i].dst == pieces[i - 1].dst + pieces[i - 1].bytes; };
+    const uint64_t bin_cap = kUpPiece;
     std::vector<std::pair<uint32_t, uint32_t>> bins;
     {
         uint64_t fill = 0;
         uint32_t first = 0;
         for (uint32_t i = 0; i < pieces.size(); ++i) {
             uint64_t start = (i > first && continues(i)) ? fill : ((fill + 255) & ~255ull);
-            if (start + pieces[i].bytes > kUpPiece && i > first) {
+            if (start + pieces[i].bytes > bin_cap && i > first) {
                 bins.push_back({first, i});
                 first = i;
                 start = 0;
@@ -896,7 +975,7 @@ int upload_segments(HostCtx& c, const std::vector<UpSeg>& segs) {
     std::atomic<int> err{0};
     const uint64_t base = c.up_issued;
     const int dev = c.bound_device;
-    auto work = [&]() {
+    auto work = [&](unsigned) {
         cudaSetDevice(dev);
         for (;;) {
             const uint64_t k = next.fetch_add(1);
@@ -926,10 +1005,7 @@ int upload_segments(HostCtx& c, const std::vector<UpSeg>& segs) {
             c.up_done[slot].store(g + 1, std::memory_order_release);  // always, so that no later bin waits forever
         }
     };
-    std::vector<std::thread> pool;
-    for (unsigned t = 1; t < nthreads; ++t) pool.emplace_back(work);
-    work();
-    for (auto& th : pool) th.join();
+    HelperPool::get().run(nthreads, work);
     c.up_issued = base + nbins;
     if (err.load()) return fail(VKM_ERR_CUDA, "staged host-to-device copy failed: %s", cudaGetErrorString(cudaGetLastError()));
     return VKM_OK;
@@ -1443,6 +1519,11 @@ int vkm_set_result_memory(int mode) {
     g_result_mode.store(mode);
     if (mode == 0) g_results.trim();
     return VKM_OK;
+}
+
+// for the library's other translation units: fn(ctx, 0) .. fn(ctx, n-1) on the helper pool
+void vkm_internal_parallel_run(unsigned n, void (*fn)(void*, unsigned), void* ctx) {
+    HelperPool::get().run(n, [&](unsigned i) { fn(ctx, i); });
 }
 
 void* vkm_host_alloc(uint64_t bytes) {
