@@ -138,6 +138,15 @@ __host__ __device__ __forceinline__ float dec_float(uint32_t e) {
 __device__ __forceinline__ bool nonfinite_bits(uint32_t b) { return (b & 0x7F800000u) == 0x7F800000u; }
 __device__ __forceinline__ uint32_t canon_bits(uint32_t b) { return b == 0x80000000u ? 0u : b; }
 
+// Programmatic dependent launch (the import's kernels are launched with the stream-serialisation attribute): the
+// first statement of every import kernel lets the NEXT kernel's CTAs become resident as this grid's CTAs retire, and
+// then waits until the PREVIOUS kernel has completed and its memory is visible.  Nothing the previous kernel wrote
+// is touched before pdl_enter() returns.  Launched without the attribute, both instructions do nothing.
+__device__ __forceinline__ void pdl_enter() {
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // Global rank (number of vertex-creating corners before corner c).
 __device__ __forceinline__ uint32_t rank_of(const ImportArgs& a, uint32_t c) {
     const uint32_t w = c >> 5;

@@ -28,6 +28,7 @@ constexpr int kThreads = 256;
 // status -> 0.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads) k_clear(ImportArgs a) {
+    pdl_enter();
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
     const uint4 ff = make_uint4(kEmpty32, kEmpty32, kEmpty32, kEmpty32);
     uint4* t1 = reinterpret_cast<uint4*>(a.table1);
@@ -60,6 +61,7 @@ __device__ __forceinline__ bool same_triplet(const int32_t* __restrict__ idx, ui
 // Specialising removes the per-corner mode/shape branching; the kernel is instruction-issue bound.
 template <int ADDR, bool MULTI>
 __global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
+    pdl_enter();
     const uint32_t ngroups = (a.ncorners + 3) >> 2;
     for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
         const uint32_t c0 = g << 2;
@@ -197,6 +199,7 @@ __device__ __forceinline__ void box_atomics(uint32_t* e, const uint32_t mn[3], c
 // Slot order follows the key attribute's index order, so the gathers are as coherent as the mesh.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads, 8) k_resolve_slots(ImportArgs a, bool write_aux) {
+    pdl_enter();
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t neutral = 0x80000000u;  // enc_float(+0): the reference's box always contains the origin
     // One thread per PAIR of slots: in mode 0 a key record owns slots (2k, 2k+1) and the odd one is only used by
@@ -274,6 +277,7 @@ __global__ void __launch_bounds__(kThreads, 8) k_resolve_slots(ImportArgs a, boo
 
 // Every occurrence of a NaN/Inf key creates a vertex (and gets index 0).
 __global__ void __launch_bounds__(kThreads) k_mark_unmatchable(ImportArgs a) {
+    pdl_enter();
     if (a.status->has_unmatchable == 0) return;
     for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < a.ncorners; c += gridDim.x * blockDim.x) {
         if (a.aux1[a.slot1[c]] == kUnmatchable) atomicOr(a.fbits + (c >> 5), 1u << (c & 31));
@@ -283,11 +287,13 @@ __global__ void __launch_bounds__(kThreads) k_mark_unmatchable(ImportArgs a) {
 // Only when value duplicates exist: the speculative flags are wrong for the later triplet of each duplicate
 // group.  Clear them, then flag the lowest corner of every distinct value key from the value table.
 __global__ void __launch_bounds__(kThreads) k_redo_flags_clear(ImportArgs a) {
+    pdl_enter();
     if (a.status->has_value_dup == 0) return;
     for (uint32_t w = blockIdx.x * blockDim.x + threadIdx.x; w < a.nwords; w += gridDim.x * blockDim.x) a.fbits[w] = 0;
 }
 
 __global__ void __launch_bounds__(kThreads) k_redo_flags_mark(ImportArgs a) {
+    pdl_enter();
     if (a.status->has_value_dup == 0) return;
     for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < a.m2; s += gridDim.x * blockDim.x) {
         const uint32_t cur = a.table2[s];
@@ -333,6 +339,7 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t x, uint32_t* t
 }
 
 __global__ void __launch_bounds__(kScanThreads) k_scan_tiles(ImportArgs a) {
+    pdl_enter();
     const uint32_t base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
     uint32_t sum = 0;
 #pragma unroll
@@ -348,6 +355,7 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_tiles(ImportArgs a) {
 // its share of lastface[0, total), and the first blocks also rank the shape boundaries straight from the
 // bitmap (so no block has to wait for another block's prefixes).
 __global__ void __launch_bounds__(kScanThreads) k_scan_finish(ImportArgs a, uint32_t ntiles) {
+    pdl_enter();
     __shared__ uint32_t red[2][32];
     uint32_t before = 0, all = 0;
     for (uint32_t i = threadIdx.x; i < ntiles; i += kScanThreads) {
@@ -413,6 +421,7 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_finish(ImportArgs a, uint
 // Final indices
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads) k_final_index(ImportArgs a) {
+    pdl_enter();
     if (import_is_clean(a)) return;  // clean import: k_write_indices ranks the slot's first corner itself
     for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < a.m1; s += gridDim.x * blockDim.x) {
         const uint32_t first = a.table1[s];
@@ -434,6 +443,7 @@ __global__ void __launch_bounds__(kThreads) k_final_index(ImportArgs a) {
 }
 
 __global__ void __launch_bounds__(kThreads) k_write_indices(ImportArgs a) {
+    pdl_enter();
     const bool clean = import_is_clean(a);
     const uint32_t ngroups = (a.ncorners + 3) >> 2;
     for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
@@ -544,6 +554,7 @@ __device__ __forceinline__ void store_vertex(float4* dst, const uint32_t k[8], f
 
 // Short schedule only: flag the first corner of every distinct triplet (speculation: the import is clean).
 __global__ void __launch_bounds__(kThreads) k_flag_firsts(ImportArgs a) {
+    pdl_enter();
     const uint32_t npairs = a.m1 >> 1;
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < npairs; p += gridDim.x * blockDim.x) {
         const uint2 cc = __ldcs(reinterpret_cast<const uint2*>(a.table1) + p);
@@ -559,6 +570,7 @@ __global__ void __launch_bounds__(kThreads) k_flag_firsts(ImportArgs a) {
 // the import with the full schedule (k_resolve_slots first).
 template <bool DETECT>
 __global__ void __launch_bounds__(kThreads, 6) k_write_vertices(ImportArgs a) {
+    pdl_enter();
     const uint32_t npairs = a.m1 >> 1;  // one thread per pair of slots, as in k_resolve_slots
     const bool fuse = import_is_clean(a);
     const bool fast = trip_is_fast(a);
@@ -650,6 +662,7 @@ __global__ void __launch_bounds__(kThreads, 6) k_write_vertices(ImportArgs a) {
 }
 
 __global__ void __launch_bounds__(kThreads) k_write_unmatchable_vertices(ImportArgs a) {
+    pdl_enter();
     if (a.status->has_unmatchable == 0) return;
     for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < a.ncorners; c += gridDim.x * blockDim.x) {
         if (a.aux1[a.slot1[c]] != kUnmatchable) continue;
@@ -690,6 +703,7 @@ __global__ void __launch_bounds__(kThreads) k_per_vertex_frames(float4* vtx, con
                                                                 const uint32_t* __restrict__ shape_off,
                                                                 const uint32_t* __restrict__ vbase, uint32_t nshapes,
                                                                 uint32_t vertex_limit, const Status* fused_status) {
+    pdl_enter();
     // import pipeline: nothing to do when k_write_vertices already produced the tangents
     if (fused_status && fused_status->has_value_dup == 0 && fused_status->has_unmatchable == 0) return;
     const uint32_t total = total_ptr ? min(*total_ptr, total_max) : total_max;

@@ -365,6 +365,25 @@ void plan_harvest(vkm_plan* p, int slot) {
     p->ev_used[slot] = false;
 }
 
+// Kernel launch of the import schedule.  With `pdl` the launch carries the programmatic-stream-serialisation
+// attribute: the grid may become resident while its predecessor in the stream drains (the predecessor's first
+// statement allows it) and blocks in pdl_enter() until that predecessor has completed -- launch latency and the
+// predecessor's tail are overlapped, the data dependency is unchanged.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_k(bool pdl, void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 int plan_enqueue(vkm_plan* p) {
     ImportArgs& a = p->args;
     cudaStream_t st = p->last_stream;
@@ -402,13 +421,21 @@ int plan_enqueue(vkm_plan* p) {
     const bool full = p->force_full || !p->assume_clean;
     p->ran_full = full;
     if (T) CU(cudaEventRecord(ev[PH_CLEAR], st));
-    k_clear<<<grid_for(std::max(a.m1, a.m2) / 4, kThreads, dev), kThreads, 0, st>>>(a);
+    // Programmatic dependent launch between the kernels of one import (not across the event records of timing mode,
+    // and not for k_clear, whose predecessor in the stream is a copy).  Only for imports whose kernels are short:
+    // there the launch gaps are a tenth of the import (1 M triangles: 0.121 -> 0.109 ms).  On long kernels it LOSES
+    // (16 M triangles: 1.02 -> 1.07 ms): the dependent grid's CTAs move in wherever a slot frees up first, so its
+    // 8-per-SM grid-stride split is no longer even and the SMs that took the extra CTAs finish late.
+    const bool P = !T && a.ncorners < (6u << 20);
+    cudaError_t le = cudaSuccess;
+    auto L = [&](cudaError_t e) { if (le == cudaSuccess) le = e; };
+    L(launch_k(false, k_clear, grid_for(std::max(a.m1, a.m2) / 4, kThreads, dev), kThreads, st, a));
     if (T) CU(cudaEventRecord(ev[PH_INSERT], st));
     {
         const unsigned g1 = grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev);
         const int addr = a.t1_mode == 0 ? (int)a.t1_sel : 3;
         const bool multi = a.nshapes > 1;
-#define VKM_K1(A, M) k_insert_triplets<A, M><<<g1, kThreads, 0, st>>>(a)
+#define VKM_K1(A, M) L(launch_k(P, k_insert_triplets<A, M>, g1, kThreads, st, a))
         switch (addr * 2 + (multi ? 1 : 0)) {
             case 0: VKM_K1(0, false); break;
             case 1: VKM_K1(0, true); break;
@@ -423,29 +450,31 @@ int plan_enqueue(vkm_plan* p) {
     }
     if (T) CU(cudaEventRecord(ev[PH_VALUES], st));
     // short schedule: the value-level proof rides along in k_write_vertices<true>; only the flag bits are set here
-    if (full) k_resolve_slots<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a, true);
-    else k_flag_firsts<<<grid_for(a.m1 / 2, kThreads, dev), kThreads, 0, st>>>(a);
+    if (full) L(launch_k(P, k_resolve_slots, grid_for(a.m1 / 2, kThreads, dev), kThreads, st, a, true));
+    else L(launch_k(P, k_flag_firsts, grid_for(a.m1 / 2, kThreads, dev), kThreads, st, a));
     if (T) CU(cudaEventRecord(ev[PH_SCAN], st));
     if (full) {
-        k_redo_flags_clear<<<grid_for(a.nwords, kThreads, dev), kThreads, 0, st>>>(a);
-        k_redo_flags_mark<<<grid_for(a.m2, kThreads, dev), kThreads, 0, st>>>(a);
-        k_mark_unmatchable<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
+        L(launch_k(P, k_redo_flags_clear, grid_for(a.nwords, kThreads, dev), kThreads, st, a));
+        L(launch_k(P, k_redo_flags_mark, grid_for(a.m2, kThreads, dev), kThreads, st, a));
+        L(launch_k(P, k_mark_unmatchable, grid_for(a.ncorners, kThreads, dev), kThreads, st, a));
     }
     const uint32_t ntiles = std::max<uint32_t>(1, (a.nwords + kScanTile - 1) / kScanTile);
-    k_scan_tiles<<<ntiles, kScanThreads, 0, st>>>(a);
-    k_scan_finish<<<ntiles, kScanThreads, 0, st>>>(a, ntiles);
+    L(launch_k(P, k_scan_tiles, ntiles, kScanThreads, st, a));
+    L(launch_k(P, k_scan_finish, ntiles, kScanThreads, st, a, ntiles));
     if (T) CU(cudaEventRecord(ev[PH_INDICES], st));
-    if (full) k_final_index<<<grid_for(a.m1, kThreads, dev), kThreads, 0, st>>>(a);
-    k_write_indices<<<grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, 0, st>>>(a);
+    if (full) L(launch_k(P, k_final_index, grid_for(a.m1, kThreads, dev), kThreads, st, a));
+    L(launch_k(P, k_write_indices, grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, st, a));
     if (T) CU(cudaEventRecord(ev[PH_VERTICES], st));
-    if (full) k_write_vertices<false><<<grid_for(a.m1 / 2, kThreads, dev, 6), kThreads, 0, st>>>(a);
-    else k_write_vertices<true><<<grid_for(a.m1 / 2, kThreads, dev, 6), kThreads, 0, st>>>(a);
-    if (full) k_write_unmatchable_vertices<<<grid_for(a.ncorners, kThreads, dev), kThreads, 0, st>>>(a);
+    if (full) L(launch_k(P, k_write_vertices<false>, grid_for(a.m1 / 2, kThreads, dev, 6), kThreads, st, a));
+    else L(launch_k(P, k_write_vertices<true>, grid_for(a.m1 / 2, kThreads, dev, 6), kThreads, st, a));
+    if (full) L(launch_k(P, k_write_unmatchable_vertices, grid_for(a.ncorners, kThreads, dev), kThreads, st, a));
     if (T) CU(cudaEventRecord(ev[PH_TANGENTS], st));
     if (full)
-        k_per_vertex_frames<0><<<grid_for(a.vertex_capacity, kThreads, dev), kThreads, 0, st>>>(
-            a.out_vtx, a.out_idx, a.lastface, &p->status.p->total_vertices, a.vertex_capacity, a.shape_off, a.vbase,
-            a.nshapes, a.vertex_capacity, p->status.p);
+        L(launch_k(P, k_per_vertex_frames<0>, grid_for(a.vertex_capacity, kThreads, dev), kThreads, st, a.out_vtx,
+                   (const uint32_t*)a.out_idx, (const uint32_t*)a.lastface, (const uint32_t*)&p->status.p->total_vertices,
+                   a.vertex_capacity, (const uint32_t*)a.shape_off, (const uint32_t*)a.vbase, a.nshapes, a.vertex_capacity,
+                   (const Status*)p->status.p));
+    if (le != cudaSuccess) return fail(VKM_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(le));
     CU(cudaEventRecord(ev[PH_COUNT], st));
     p->slot_busy[slot] = true;
     p->seq++;
