@@ -451,7 +451,7 @@ __global__ void __launch_bounds__(kThreads) k_write_indices(ImportArgs a) {
         uint32_t s[4] = {0, 0, 0, 0};
         const bool full = (c0 + 4 <= a.ncorners);
         if (full) {
-            const uint4 q = *reinterpret_cast<const uint4*>(a.slot1 + c0);
+            const uint4 q = __ldcs(reinterpret_cast<const uint4*>(a.slot1 + c0));
             s[0] = q.x; s[1] = q.y; s[2] = q.z; s[3] = q.w;
         } else {
             for (int i = 0; i < 4 && c0 + i < a.ncorners; ++i) s[i] = a.slot1[c0 + i];
@@ -482,7 +482,7 @@ __global__ void __launch_bounds__(kThreads) k_write_indices(ImportArgs a) {
             if (gv < a.vertex_capacity) atomicMax(a.lastface + gv, c / 3 + 1);
         }
         if (full) {
-            *reinterpret_cast<uint4*>(a.out_idx + c0) = make_uint4(li[0], li[1], li[2], li[3]);
+            __stcs(reinterpret_cast<uint4*>(a.out_idx + c0), make_uint4(li[0], li[1], li[2], li[3]));
         } else {
             for (int i = 0; i < 4 && c0 + i < a.ncorners; ++i) a.out_idx[c0 + i] = li[i];
         }
