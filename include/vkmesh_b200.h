@@ -220,12 +220,35 @@ typedef struct vkm_plan_result {
 int vkm_plan_create(const vkm_plan_desc* desc, vkm_plan** out);
 void vkm_plan_destroy(vkm_plan* plan);
 /* Enqueues the whole import on `stream` (a cudaStream_t; NULL = the plan's own stream).  All pointers are
- * device pointers except shape_corner_offsets (host).  Asynchronous. */
+ * device pointers except shape_corner_offsets (host).  Asynchronous.
+ *   - Alignment (checked, VKM_ERR_INVALID_ARG): d_idx_vnt 16 bytes, d_uv 8 bytes, d_pos / d_nrm 4 bytes -- the kernels
+ *     read them with 128-/64-bit loads.  cudaMalloc results qualify; a sub-range of a packed arena may not.
+ *   - A plan holds ONE set of outputs and ONE status block.  Several imports may be queued on one stream before
+ *     vkm_plan_finish (bench.py does, to time back-to-back imports), but only the LAST one's results and status
+ *     are observable; an error or a failed speculation in an earlier queued import goes unnoticed.  Callers that
+ *     consume every result call vkm_plan_finish after every vkm_plan_import.
+ *   - Schedules.  While the plan expects a "clean" mesh (no two distinct (v,vn,vt) triplets with equal values, no
+ *     NaN/Inf attribute: true for nearly every mesh, assumed for a new plan) it launches the short record
+ *     schedule, which also proves the assumption; if the proof fails, vkm_plan_finish discards that run and
+ *     launches the general schedule once (vkm_plan_stats.mis_speculated).  After a non-clean import the general
+ *     schedule runs first.  All schedules give identical results. */
 int vkm_plan_import(vkm_plan* plan, const float* d_pos, uint64_t np, const float* d_nrm, uint64_t nn,
                     const float* d_uv, uint64_t nt, const int32_t* d_idx_vnt, const uint64_t* shape_corner_offsets,
                     uint32_t nshapes, void* stream);
 /* Waits for the import, checks the device status word and fills `result`. */
 int vkm_plan_finish(vkm_plan* plan, vkm_plan_result* result);
+/* What vkm_plan_finish had to do for the last import (no reference counterpart: the reference has one code path). */
+typedef struct vkm_plan_stats {
+    uint32_t runs;            /* schedules launched (1 = the first one stood) */
+    uint32_t schedule;        /* the one whose results stood: 0 record (clean speculation), 1 short general, 2 full general */
+    uint32_t mis_speculated;  /* 1 = a clean-speculating run was discarded because the mesh was not clean */
+    uint32_t table_overflows; /* re-runs because a hash table was too small or its keys clustered */
+    uint32_t reseeds;         /* hash generation changes among those re-runs */
+    uint32_t hash_seed;       /* hash generation in force */
+} vkm_plan_stats;
+int vkm_plan_get_stats(const vkm_plan* plan, vkm_plan_stats* out);
+/* The same for the plan behind the host entry points (vkm_import_shapes and friends; the calling thread's last call). */
+int vkm_last_import_stats(vkm_plan_stats* out);
 /* When enabled, vkm_plan_import records CUDA events between phases (costs a few microseconds). */
 void vkm_plan_set_timing(vkm_plan* plan, int enabled);
 /* Names of the phases reported in vkm_plan_result.phase_ms (NULL past the last). */

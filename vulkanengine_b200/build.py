@@ -36,6 +36,15 @@ def up_to_date() -> bool:
     return all(os.path.getmtime(f) <= t for f in _deps())
 
 
+def build_variant(name: str, defines) -> str:
+    """An experimental build with extra -D flags into lib/variants/ (kernel experiments; never the shipped library)."""
+    out_dir = os.path.join(LIB_DIR, "variants")
+    os.makedirs(out_dir, exist_ok=True)
+    out = os.path.join(out_dir, f"libvkmesh_{name}.so")
+    subprocess.check_call([os.environ.get("NVCC", "nvcc"), *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-o", out, *sources()])
+    return out
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and up_to_date():
         return LIB_PATH

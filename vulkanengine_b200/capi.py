@@ -30,7 +30,7 @@ SYMBOLS = [
     "vkm_e3dm_write", "vkm_e3dm_read", "vkm_e3dm_free", "vkm_parse_obj", "vkm_free_obj_streams",
     "vkm_import_obj_text", "vkm_free_obj_import", "vkm_generate_plane_config", "vkm_generate_cube_config",
     "vkm_plan_create", "vkm_plan_destroy", "vkm_plan_import", "vkm_plan_finish", "vkm_plan_set_timing",
-    "vkm_plan_phase_name", "vkm_generate_tangents_dev", "vkm_generate_normals_dev",
+    "vkm_plan_phase_name", "vkm_plan_get_stats", "vkm_last_import_stats", "vkm_generate_tangents_dev", "vkm_generate_normals_dev",
     "vkm_generate_tangents_dev_noalloc",
     "vkm_rangealloc_create", "vkm_rangealloc_destroy", "vkm_rangealloc_alloc", "vkm_rangealloc_free",
     "vkm_rangealloc_free_space", "vkm_pool_create", "vkm_pool_destroy", "vkm_pool_vertex_buffer",
@@ -86,6 +86,14 @@ class PlanDesc(C.Structure):
                 ("max_attrib", C.c_uint64), ("max_shapes", C.c_uint32)]
 
 
+class PlanStats(C.Structure):
+    _fields_ = [("runs", C.c_uint32), ("schedule", C.c_uint32), ("mis_speculated", C.c_uint32),
+                ("table_overflows", C.c_uint32), ("reseeds", C.c_uint32), ("hash_seed", C.c_uint32)]
+
+    def as_dict(self):
+        return {k: int(getattr(self, k)) for k, _ in self._fields_}
+
+
 class PlanResult(C.Structure):
     _fields_ = [("total_vertices", C.c_uint64), ("total_indices", C.c_uint64), ("d_vertices", C.c_void_p),
                 ("d_indices", C.c_void_p), ("shape_vertex_offsets", C.POINTER(C.c_uint32)),
@@ -104,7 +112,7 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.LIB_PATH
+    path = os.environ.get("VKM_LIB_PATH") or _build.LIB_PATH  # (override: experimental builds of the same ABI)
     if not os.path.exists(path):
         path = _build.build()
     L = C.CDLL(path)
@@ -152,6 +160,8 @@ def lib():
     L.vkm_plan_finish.restype = C.c_int
     L.vkm_plan_finish.argtypes = [C.c_void_p, C.POINTER(PlanResult)]
     L.vkm_plan_set_timing.argtypes = [C.c_void_p, C.c_int]
+    L.vkm_plan_get_stats.argtypes = [C.c_void_p, C.POINTER(PlanStats)]
+    L.vkm_last_import_stats.argtypes = [C.POINTER(PlanStats)]
     L.vkm_plan_phase_name.restype = C.c_char_p
     L.vkm_plan_phase_name.argtypes = [C.c_int]
     for fn in (L.vkm_generate_tangents_dev, L.vkm_generate_normals_dev):
@@ -460,6 +470,13 @@ def download(device: int, ptr: int, dtype, count: int) -> np.ndarray:
     return out
 
 
+def last_import_stats() -> dict:
+    """What the library had to do for this thread's last host-entry import (schedule, re-runs, reseeds)."""
+    st = PlanStats()
+    _check(lib().vkm_last_import_stats(C.byref(st)))
+    return st.as_dict()
+
+
 class Plan:
     """vkm_plan: device-resident import with preallocated scratch and outputs."""
 
@@ -498,6 +515,11 @@ class Plan:
             ext = np.array(list(e.center) + list(e.min_extents) + list(e.max_extents), np.float32)
             out.append(ShapeResult(v, ix, ext))
         return out
+
+    def stats(self) -> dict:
+        st = PlanStats()
+        _check(lib().vkm_plan_get_stats(self.h, C.byref(st)))
+        return st.as_dict()
 
     def phase_names(self):
         names, i = [], 0

@@ -53,6 +53,15 @@ struct ImportArgs {
     uint32_t* ext_enc;  // [nshapes * 6] order-encoded min xyz, max xyz
     uint32_t* vbase;    // [nshapes + 1] first global vertex id of every shape
     uint32_t* lastface; // [vertex capacity] 1 + highest face id that references the vertex
+    // record schedule (vkm_records.cuh): one 16-byte record per key-attribute record + a small hashed side table
+    uint32_t* rfirst;    // [nkey] first (lowest) corner of the key record's first variant; all-ones = unclaimed
+    uint2* ident;        // [nkey] that variant's other two indices (a, b); all-ones = not published yet
+    uint32_t nkey;       // records of the key attribute (t1_sel)
+    uint32_t* sec_first; // [msec] side table: first corner of a triplet that is not its key record's first variant
+    uint32_t* sec_last;  // [msec] its last corner
+    uint32_t msec;
+    uint32_t* vid_of;    // [nkey + msec] local vertex index of every slot (written by the vertex pass)
+    uint32_t seed;       // hash generation of this run (see hash_triplet)
     // outputs
     uint32_t* out_idx;  // [ncorners] per-shape local indices
     float4* out_vtx;    // [vertex capacity * 4]
@@ -69,10 +78,12 @@ __device__ __forceinline__ uint64_t mix64(uint64_t x) {
     return x;
 }
 
-__device__ __forceinline__ uint64_t hash_triplet(uint32_t v, uint32_t n, uint32_t t, uint32_t shape) {
+// `seed` is the plan's hash generation: 0 until a table overflows at a size that should have held the mesh (keys
+// clustering in THIS hash), then bumped so that the re-run spreads them differently.
+__device__ __forceinline__ uint64_t hash_triplet(uint32_t v, uint32_t n, uint32_t t, uint32_t shape, uint32_t seed) {
     const uint64_t a = (uint64_t)v | ((uint64_t)n << 32);
     const uint64_t b = (uint64_t)t | ((uint64_t)shape << 32);
-    return mix64(a ^ mix64(b + 0x9e3779b97f4a7c15ull));
+    return mix64(a ^ mix64(b + 0x9e3779b97f4a7c15ull + 0xd6e8feb86659fd93ull * seed));
 }
 
 // Range reduction without a power-of-two table: floor(x * m / 2^32).
@@ -97,11 +108,11 @@ __device__ __forceinline__ uint32_t home_slot(const ImportArgs& a, uint32_t v, u
         const uint32_t key = a.t1_sel == 0 ? v : (a.t1_sel == 1 ? n : t);
         return key * a.t1_scale;  // < np|nn|nt * scale <= m1 (host guarantees no 32-bit overflow)
     }
-    return reduce32((uint32_t)hash_triplet(v, n, t, sh), a.m1);
+    return reduce32((uint32_t)hash_triplet(v, n, t, sh, a.seed), a.m1);
 }
 
-__device__ __forceinline__ uint64_t hash_key8(const uint32_t k[8], uint32_t shape) {
-    uint64_t h = mix64(((uint64_t)k[0] | ((uint64_t)k[1] << 32)) + 0x9e3779b97f4a7c15ull * (shape + 1));
+__device__ __forceinline__ uint64_t hash_key8(const uint32_t k[8], uint32_t shape, uint32_t seed) {
+    uint64_t h = mix64(((uint64_t)k[0] | ((uint64_t)k[1] << 32)) + 0x9e3779b97f4a7c15ull * (shape + 1) + 0xd6e8feb86659fd93ull * seed);
     h = mix64(h ^ ((uint64_t)k[2] | ((uint64_t)k[3] << 32)));
     h = mix64(h ^ ((uint64_t)k[4] | ((uint64_t)k[5] << 32)));
     h = mix64(h ^ ((uint64_t)k[6] | ((uint64_t)k[7] << 32)));

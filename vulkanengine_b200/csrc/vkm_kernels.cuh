@@ -102,7 +102,7 @@ __global__ void __launch_bounds__(kThreads) k_insert_triplets(ImportArgs a) {
             if (ADDR == 0) s = v * 2;
             else if (ADDR == 1) s = n * 2;
             else if (ADDR == 2) s = t * 2;
-            else s = reduce32((uint32_t)hash_triplet(v, n, t, sh), a.m1);
+            else s = reduce32((uint32_t)hash_triplet(v, n, t, sh, a.seed), a.m1);
             bool ok = false;
             for (int probe = 0; probe < kMaxProbe; ++probe) {
                 uint32_t cur = __ldcg(a.table1 + s);
@@ -156,7 +156,7 @@ __device__ __forceinline__ bool same_value_key(const ImportArgs& a, uint32_t occ
 
 __device__ __forceinline__ uint32_t insert_value(const ImportArgs& a, uint32_t c, const uint32_t k[8], uint32_t sh,
                                                  uint32_t sh_begin, uint32_t sh_end) {
-    const uint64_t h = hash_key8(k, sh);
+    const uint64_t h = hash_key8(k, sh, a.seed);
     const uint32_t cmask = (a.cbits >= 32) ? 0xFFFFFFFFu : ((1u << a.cbits) - 1u);
     const uint32_t tag = (a.cbits >= 32) ? 0u : ((uint32_t)(h >> 32) >> a.cbits) << a.cbits;  // high (32 - cbits) bits
     const uint32_t mine = tag | c;
@@ -354,7 +354,7 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_tiles(ImportArgs a) {
 // from the few thousand tile sums (cheaper than a third launch), writes its tile's exclusive prefixes, zeroes
 // its share of lastface[0, total), and the first blocks also rank the shape boundaries straight from the
 // bitmap (so no block has to wait for another block's prefixes).
-__global__ void __launch_bounds__(kScanThreads) k_scan_finish(ImportArgs a, uint32_t ntiles) {
+__global__ void __launch_bounds__(kScanThreads) k_scan_finish(ImportArgs a, uint32_t ntiles, bool reset_lastface) {
     pdl_enter();
     __shared__ uint32_t red[2][32];
     uint32_t before = 0, all = 0;
@@ -400,7 +400,7 @@ __global__ void __launch_bounds__(kScanThreads) k_scan_finish(ImportArgs a, uint
         run += pc[i];
     }
     // lastface[0, total) = 0
-    const uint32_t nv = min(all, a.vertex_capacity);
+    const uint32_t nv = reset_lastface ? min(all, a.vertex_capacity) : 0u;  // (the record schedule keeps no lastface)
     for (uint32_t i = blockIdx.x * kScanThreads + threadIdx.x; i < nv; i += ntiles * kScanThreads) a.lastface[i] = 0;
     // shape boundaries: one warp per shape, ranks computed from tile sums + the bitmap itself
     const uint32_t gwarp = (blockIdx.x * kScanThreads + threadIdx.x) >> 5, nwarps = (ntiles * kScanThreads) >> 5;

@@ -1,0 +1,459 @@
+// Record schedule of the import path (sm_100a): the schedule an import runs with while the plan expects a
+// "clean" mesh (no two distinct triplets with equal values, no NaN/Inf key).  SURVEY.md section 8(a) rows A2-A5.
+//
+// The general schedule (vkm_kernels.cuh) keeps a hashed u32 table and decides "same triplet" by a second, dependent
+// read of the occupant's triplet from the index stream.  Here every record k of the KEY attribute (the largest of
+// the v / vn / vt arrays) owns slot k directly -- no hashing, no probing:
+//     rfirst[k]  u32    lowest corner seen so far of the record's first variant   (dense: 8 slots per sector)
+//     ident[k]   uint2  (a, b) = that variant's other two indices, published by the thread that claimed rfirst[k]
+// so a corner decides from two loads whose addresses it knows from its own indices, and the four corners of a thread
+// have all eight loads in flight together.  Until the claimer's identity store is visible (a window of one round
+// trip) a reader falls back to the general schedule's exact compare through the index stream.  Triplets that are not
+// the first variant of their key record (same v, other vn/vt: seams) go to a small hashed side table.  `first` is
+// lowered with atomicMin: integer, so the result does not depend on scheduling.  A slot (key record or side-table
+// entry) is one distinct (shape, v, n, t).  Measured on B200: 16-byte {first,a,b,last} records claimed with a
+// 128-bit CAS cost 61 M L2 atomics per 50 M corners and ran 1.6x slower than this layout.
+//
+//   k_clear_records      slots / side table / fingerprint table -> empty, bitmap -> 0, boxes, status
+//   k_insert_records     corner domain: 3 x 128-bit index loads per 4 corners, slot per corner
+//   k_flag_records       slot domain: flag bit of every slot's first corner
+//   (k_scan_tiles / k_scan_finish of vkm_kernels.cuh: stable first-occurrence ranks)
+//   k_rank_records       slot domain: vid_of[slot] = local vertex index
+//   k_write_indices_rec  corner domain: out_idx[c] = vid_of[slot[c]] (a gather) + atomicMax(last face of the vertex)
+//   k_write_vertices_rec slot domain: gather 8 floats, box, NaN/Inf screen, fingerprint of the value key (the proof
+//                        that the import IS clean), tangent of the vertex's last triangle, 64-byte record
+//
+// If the status block says the mesh was not clean (or a table overflowed), vkm_plan_finish re-runs the import
+// with the general schedule of vkm_kernels.cuh; results are only observable after finish.
+#pragma once
+
+#include "vkm_kernels.cuh"
+
+namespace vkm {
+
+// KEY = which index addresses the slot (0: v, 1: vn, 2: vt); (a, b) are the other two in v, vn, vt order.
+template <int KEY>
+__device__ __forceinline__ void split_triplet(uint32_t v, uint32_t n, uint32_t t, uint32_t& k, uint32_t& x, uint32_t& y) {
+    if (KEY == 0) { k = v; x = n; y = t; }
+    else if (KEY == 1) { k = n; x = v; y = t; }
+    else { k = t; x = v; y = n; }
+}
+template <int KEY>
+__device__ __forceinline__ void join_triplet(uint32_t k, uint32_t x, uint32_t y, uint32_t& v, uint32_t& n, uint32_t& t) {
+    if (KEY == 0) { v = k; n = x; t = y; }
+    else if (KEY == 1) { n = k; v = x; t = y; }
+    else { t = k; v = x; n = y; }
+}
+
+__global__ void __launch_bounds__(kThreads) k_clear_records(ImportArgs a) {
+    pdl_enter();
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    const uint4 ff = make_uint4(kEmpty32, kEmpty32, kEmpty32, kEmpty32);
+    // (the plan's arrays are padded, so whole uint4 stores past nkey stay in bounds)
+    uint4* p1 = reinterpret_cast<uint4*>(a.rfirst);
+    for (uint32_t i = tid; i < (a.nkey + 3) / 4; i += nth) p1[i] = ff;
+    uint4* p2 = reinterpret_cast<uint4*>(a.ident);
+    for (uint32_t i = tid; i < (a.nkey + 1) / 2; i += nth) p2[i] = ff;
+    for (uint32_t i = tid; i < a.msec; i += nth) a.sec_first[i] = kEmpty32;
+    uint4* t2 = reinterpret_cast<uint4*>(a.table2);
+    for (uint32_t i = tid; i < (a.m2 >> 2); i += nth) t2[i] = ff;  // m2 is a multiple of 8 here
+    for (uint32_t i = tid; i <= a.nwords; i += nth) a.fbits[i] = 0;
+    for (uint32_t i = tid; i < a.nshapes * 6u; i += nth) a.ext_enc[i] = 0x80000000u;
+    if (tid < sizeof(Status) / 4) reinterpret_cast<uint32_t*>(a.status)[tid] = 0;
+}
+
+// Side table: triplets whose key record is owned by another variant (or by another shape).  Same protocol as
+// the general schedule's triplet table: CAS claim, exact compare against the occupant's own triplet, atomicMin.
+// (scalar arguments: a by-reference ImportArgs would force a local-memory copy of the kernel parameters)
+__device__ __noinline__ uint32_t insert_side(uint32_t* sec_first, uint32_t msec, uint32_t seed, const int32_t* idx,
+                                             uint32_t c, uint32_t v, uint32_t n, uint32_t t, uint32_t sh,
+                                             uint32_t sh_begin, uint32_t sh_end) {
+    uint32_t s = reduce32((uint32_t)hash_triplet(v, n, t, sh, seed), msec);
+    for (int probe = 0; probe < kMaxProbe; ++probe) {
+        uint32_t cur = __ldcg(sec_first + s);
+        if (cur == kEmpty32) {
+            const uint32_t prev = atomicCAS(sec_first + s, kEmpty32, c);
+            cur = (prev == kEmpty32) ? c : prev;
+        }
+        if (cur == c || same_triplet(idx, cur, v, n, t, sh_begin, sh_end)) {
+            if (cur > c) atomicMin(sec_first + s, c);
+            return s;
+        }
+        s = (s + 1 == msec) ? 0 : s + 1;
+    }
+    return kEmpty32;  // table full
+}
+
+#ifndef VKM_REC_MINB
+#define VKM_REC_MINB 4
+#endif
+// Per thread and iteration: 4 consecutive corners = 48 bytes of the index stream = three 128-bit loads.  An
+// iteration costs three memory round trips, not one per corner: (1) the index words (prefetched into L2 four
+// iterations ahead), (2) the slots' first-corner and identity words, all eight loads in flight together, (3) the
+// claims of whichever slots were empty, all issued before the first result is used.  (Measured and dropped: staging
+// the index words through a per-thread cp.async ring in shared memory, 0.28 -> 0.38 ms; 16-byte AoS records.)
+template <int KEY, bool MULTI>
+__global__ void __launch_bounds__(kThreads, VKM_REC_MINB) k_insert_records(ImportArgs a) {
+    pdl_enter();
+    const uint32_t ngroups = (a.ncorners + 3) >> 2;
+    // Blocked, not grid-strided: every CTA walks ONE contiguous piece of the stream front to back.  With a grid stride
+    // the whole grid sweeps a window of ~1 M consecutive corners at once, so all the corners that share a vertex (a
+    // few thousand corners apart in a coherent mesh) meet their slot unclaimed at the same moment: measured 3.1 claim
+    // attempts and 2 atomicMin per vertex.  Walking in order, the later ones arrive after the claim is visible and
+    // need no atomic at all.
+    const uint32_t per_cta = (uint32_t)(((uint64_t)ngroups + gridDim.x - 1) / gridDim.x);
+    const uint32_t g_end = min(ngroups, (blockIdx.x + 1) * per_cta);
+    const uint32_t stride = blockDim.x;
+    for (uint32_t g = blockIdx.x * per_cta + threadIdx.x; g < g_end; g += stride) {
+        const uint32_t c0 = g << 2;
+        int32_t w[12];
+        if (c0 + 4 <= a.ncorners) {
+            const int4* src = reinterpret_cast<const int4*>(a.idx + 3ull * c0);
+            const int4 x = __ldg(src), y = __ldg(src + 1), z = __ldg(src + 2);
+            w[0] = x.x; w[1] = x.y; w[2] = x.z; w[3] = x.w;
+            w[4] = y.x; w[5] = y.y; w[6] = y.z; w[7] = y.w;
+            w[8] = z.x; w[9] = z.y; w[10] = z.z; w[11] = z.w;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 12; ++i) w[i] = (c0 + i / 3 < a.ncorners) ? __ldg(a.idx + 3ull * c0 + i) : -1;
+        }
+        if (g + 4 * stride < g_end) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.idx + 12ull * (g + 4 * stride)));
+        uint32_t key[4], oa[4], ob[4], f[4];
+        uint2 id[4];
+        bool valid[4], tried[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t v = (uint32_t)w[3 * i], n = (uint32_t)w[3 * i + 1], t = (uint32_t)w[3 * i + 2];
+            valid[i] = (c0 + i < a.ncorners) && v < a.np && n < a.nn && t < a.nt;  // negative ints are huge as unsigned
+            split_triplet<KEY>(v, n, t, key[i], oa[i], ob[i]);
+            if (!valid[i]) key[i] = 0;
+            f[i] = __ldcg(a.rfirst + key[i]);
+            id[i] = __ldcg(a.ident + key[i]);
+        }
+        // claims: a corner that saw an unclaimed slot tries to become its first corner; f[i] becomes what the slot held
+        // before (still all-ones: claimed).  Two corners of this thread with one key: the second claim fails and
+        // returns the first corner.
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            tried[i] = valid[i] && f[i] == kEmpty32;
+            if (tried[i]) f[i] = atomicCAS(a.rfirst + key[i], kEmpty32, c0 + i);
+        }
+        uint32_t sh = 0, sh_begin = 0, sh_end = a.ncorners;
+        if (MULTI) {
+            sh = find_shape(a.shape_off, a.nshapes, min(c0, a.ncorners - 1));
+            sh_begin = a.shape_off[sh];
+            sh_end = a.shape_off[sh + 1];
+        }
+        uint32_t slots[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t c = c0 + i;
+            slots[i] = 0;
+            if (c >= a.ncorners) continue;
+            if (!valid[i]) {
+                a.status->bad_index = 1;
+                continue;
+            }
+            if (MULTI && c >= sh_end) {
+                sh = find_shape(a.shape_off, a.nshapes, c);
+                sh_begin = a.shape_off[sh];
+                sh_end = a.shape_off[sh + 1];
+            }
+            if (tried[i] && f[i] == kEmpty32) {  // claimed: publish the variant's identity
+                __stcg(a.ident + key[i], make_uint2(oa[i], ob[i]));
+                slots[i] = key[i];
+                continue;
+            }
+            // identity not published when it was read (the slot was claimed in this very moment, typically by a
+            // neighbouring corner of this warp): compare with the claimer's own triplet in the index stream, which is
+            // exact and, for a neighbour, an L1 hit
+            const uint2 q = id[i];
+            uint32_t v, n, t;
+            join_triplet<KEY>(key[i], oa[i], ob[i], v, n, t);
+            bool match;
+            if (q.x != kEmpty32) match = (q.x == oa[i] && q.y == ob[i] && (!MULTI || (f[i] >= sh_begin && f[i] < sh_end)));
+            else match = same_triplet(a.idx, f[i], v, n, t, sh_begin, sh_end);
+            if (match) {
+                if (c < f[i]) atomicMin(a.rfirst + key[i], c);
+                slots[i] = key[i];
+            } else {
+                const uint32_t s2 = insert_side(a.sec_first, a.msec, a.seed, a.idx, c, v, n, t, sh, sh_begin, sh_end);
+                if (s2 == kEmpty32) a.status->overflow1 = 1;
+                else slots[i] = a.nkey + s2;
+            }
+        }
+        if (c0 + 4 <= a.ncorners) {
+            *reinterpret_cast<uint4*>(a.slot1 + c0) = make_uint4(slots[0], slots[1], slots[2], slots[3]);
+        } else {
+            for (int i = 0; i < 4 && c0 + i < a.ncorners; ++i) a.slot1[c0 + i] = slots[i];
+        }
+    }
+}
+
+// First corner of slot s (kEmpty32 = unused).
+__device__ __forceinline__ uint32_t slot_first(const ImportArgs& a, uint32_t s) {
+    return (s < a.nkey) ? __ldg(a.rfirst + s) : __ldg(a.sec_first + (s - a.nkey));
+}
+
+// The slot-domain helper passes handle FOUR key slots per thread (one 128-bit load of rfirst): with one 4-byte load per
+// thread they spend their time waiting for that single load (ncu: 49 % of the samples on it).
+// Flag the first corner of every slot (speculation: the import is clean, so every distinct triplet is a vertex).
+__global__ void __launch_bounds__(kThreads) k_flag_records(ImportArgs a) {
+    pdl_enter();
+    const uint32_t nq = (a.nkey + 3) >> 2, tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    for (uint32_t q = tid; q < nq; q += nth) {
+        const uint4 c4 = __ldcs(reinterpret_cast<const uint4*>(a.rfirst) + q);  // padding past nkey is all-ones
+        const uint32_t c[4] = {c4.x, c4.y, c4.z, c4.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (4 * q + i < a.nkey && c[i] < a.ncorners) atomicOr(a.fbits + (c[i] >> 5), 1u << (c[i] & 31));
+    }
+    for (uint32_t s = tid; s < a.msec; s += nth) {
+        const uint32_t c = __ldcs(a.sec_first + s);
+        if (c < a.ncorners) atomicOr(a.fbits + (c >> 5), 1u << (c & 31));  // kEmpty32 >= ncorners
+    }
+}
+
+// vid_of[slot] = the slot's GLOBAL vertex id (its rank among all vertex-creating corners; kEmpty32 for unused slots).
+// The index pass subtracts the shape's base, which it tracks per thread anyway.
+__global__ void __launch_bounds__(kThreads) k_rank_records(ImportArgs a) {
+    pdl_enter();
+    const uint32_t nq = (a.nkey + 3) >> 2, tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    for (uint32_t q = tid; q < nq; q += nth) {
+        const uint4 c4 = __ldg(reinterpret_cast<const uint4*>(a.rfirst) + q);
+        const uint32_t c[4] = {c4.x, c4.y, c4.z, c4.w};
+        uint32_t bits[4], pre[4], vid[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {  // all eight gathers in flight
+            const uint32_t w = min(c[i], a.ncorners - 1) >> 5;
+            bits[i] = a.fbits[w];
+            pre[i] = a.fprefix[w];
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            vid[i] = kEmpty32;
+            if (c[i] < a.ncorners) {
+                vid[i] = pre[i] + __popc(bits[i] & ((1u << (c[i] & 31)) - 1u));
+            }
+        }
+        if (4 * q + 4 <= a.nkey) {
+            *reinterpret_cast<uint4*>(a.vid_of + 4 * q) = make_uint4(vid[0], vid[1], vid[2], vid[3]);
+        } else {
+            for (int i = 0; i < 4 && 4 * q + i < a.nkey; ++i) a.vid_of[4 * q + i] = vid[i];
+        }
+    }
+    for (uint32_t s = tid; s < a.msec; s += nth) {
+        const uint32_t c = __ldg(a.sec_first + s);
+        uint32_t vid = kEmpty32;
+        if (c < a.ncorners) vid = rank_of(a, c);
+        a.vid_of[a.nkey + s] = vid;
+    }
+}
+
+// Corner domain: the index buffer is a gather of the slots' vertex indices; the vertex's last triangle is an atomicMax.
+// (Measured and dropped: two groups of four corners per thread, 0.134 -> 0.162 ms.)
+template <bool MULTI>
+__global__ void __launch_bounds__(kThreads) k_write_indices_rec(ImportArgs a) {
+    pdl_enter();
+    const uint32_t nslots = a.nkey + a.msec;
+    const uint32_t ngroups = (a.ncorners + 3) >> 2;
+    for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < ngroups; g += gridDim.x * blockDim.x) {
+        const uint32_t c0 = g << 2;
+        uint32_t s[4] = {0, 0, 0, 0}, li[4];
+        const bool full = (c0 + 4 <= a.ncorners);
+        if (full) {
+            const uint4 q = __ldcs(reinterpret_cast<const uint4*>(a.slot1 + c0));
+            s[0] = q.x; s[1] = q.y; s[2] = q.z; s[3] = q.w;
+        } else {
+            for (int i = 0; i < 4 && c0 + i < a.ncorners; ++i) s[i] = a.slot1[c0 + i];
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) li[i] = __ldg(a.vid_of + min(s[i], nslots - 1));
+        uint32_t sh = 0, sh_end = a.ncorners, base = 0;
+        if (MULTI) {
+            sh = find_shape(a.shape_off, a.nshapes, min(c0, a.ncorners - 1));
+            sh_end = a.shape_off[sh + 1];
+            base = a.vbase[sh];
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t c = c0 + i;
+            if (c >= a.ncorners) break;
+            if (MULTI && c >= sh_end) {
+                sh = find_shape(a.shape_off, a.nshapes, c);
+                sh_end = a.shape_off[sh + 1];
+                base = a.vbase[sh];
+            }
+            // a later corner of this thread that names the same vertex raises the same word higher: leave it to that one
+            bool later = false;
+#pragma unroll
+            for (int j = i + 1; j < 4; ++j) later |= (s[j] == s[i] && c0 + j < sh_end);
+            const uint32_t gv = li[i];
+            if (!later && gv < a.vertex_capacity) atomicMax(a.lastface + gv, c / 3 + 1);
+            li[i] = gv - base;  // index local to the shape
+        }
+        if (full) {
+            __stcs(reinterpret_cast<uint4*>(a.out_idx + c0), make_uint4(li[0], li[1], li[2], li[3]));
+        } else {
+            for (int i = 0; i < 4 && c0 + i < a.ncorners; ++i) a.out_idx[c0 + i] = li[i];
+        }
+    }
+}
+
+// The clean-import proof of the record schedule: every distinct triplet's canonical 8-float key leaves a 32-bit
+// fingerprint in a bucketed table (bucket = one 32-byte sector = 8 words, read with one 256-bit load).  Two EQUAL keys
+// hash to the same bucket sequence and the same fingerprint, and the later of them is guaranteed to see the earlier one
+// (a claim at word j has looked at every word before j, either in its snapshot or as the value its failed CAS
+// returned, and words never change once set): it raises has_value_dup, and vkm_plan_finish re-runs the import with
+// the general schedule, which decides exactly.  Two DIFFERENT keys with one fingerprint in one bucket (about
+// U * 4 / 2^32 per import) only cost that re-run, never a wrong result.  Against linear probing over single words
+// this needs one round trip for the whole bucket and, at load 1/2, almost never a second bucket, so the lanes of
+// a warp stay together.
+__device__ __forceinline__ void probe_fingerprint(const ImportArgs& a, const uint32_t kc[8], uint32_t sh) {
+    const uint64_t h = hash_key8(kc, sh, a.seed);
+    uint32_t fp = (uint32_t)(h >> 32);
+    if (fp == kEmpty32) fp = 0xFFFFFFFEu;
+    const uint32_t nb = a.m2 >> 3;
+    uint32_t b = reduce32((uint32_t)h, nb);
+    for (int probe = 0; probe < 256; ++probe) {
+        uint32_t* base = a.table2 + 8ull * b;
+        uint32_t w[8];
+        asm volatile("ld.global.cg.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                     : "l"(base));
+        bool seen = false;
+        uint32_t empties = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            seen |= (w[j] == fp);
+            empties |= (w[j] == kEmpty32 ? 1u : 0u) << j;
+        }
+        // ONE claim per lane at the lane's own first empty word (a per-word loop would make the warp walk all eight
+        // words one atomic round trip at a time); a second turn only when another thread took that word meanwhile
+        bool done = false;
+        while (!seen && !done && empties) {
+            const int j = __ffs(empties) - 1;
+            const uint32_t prev = atomicCAS(base + j, kEmpty32, fp);
+            if (prev == kEmpty32) done = true;
+            else if (prev == fp) seen = true;
+            empties &= empties - 1;
+        }
+        if (seen) {
+            a.status->has_value_dup = 1;
+            return;
+        }
+        if (done) return;
+        b = (b + 1 == nb) ? 0 : b + 1;
+    }
+    a.status->overflow2 = 1;
+}
+
+// (v, vt) of corner `c`, whose slot is `s`: from the slot's identity when it is a key record, else from the index stream.
+template <int KEY>
+__device__ __forceinline__ void corner_v_t(const ImportArgs& a, uint32_t s, uint32_t c, uint32_t& v, uint32_t& t) {
+    if (s < a.nkey) {
+        const uint2 ab = __ldg(a.ident + s);
+        if (KEY == 0) { v = s; t = ab.y; }
+        else if (KEY == 1) { v = ab.x; t = ab.y; }
+        else { t = s; v = ab.x; }
+    } else {
+        const int32_t* o = a.idx + 3ull * min(c, a.ncorners - 1);
+        v = (uint32_t)__ldg(o);
+        t = (uint32_t)__ldg(o + 2);
+    }
+}
+
+#ifndef VKM_VTX_MINB
+#define VKM_VTX_MINB 6
+#endif
+// Slot domain.  Also the pass that PROVES the import clean (NaN/Inf screen + fingerprint of every value key).
+template <int KEY, bool MULTI>
+__global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(ImportArgs a) {
+    pdl_enter();
+    const uint32_t nslots = a.nkey + a.msec;
+    const uint32_t padded = (nslots + 31) & ~31u;  // whole warps for the box reduction
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t neutral = 0x80000000u;
+    for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < padded; s += gridDim.x * blockDim.x) {
+        uint32_t first = kEmpty32, lid = kEmpty32, v = 0, n = 0, t = 0;
+        if (s < a.nkey) {
+            first = __ldg(a.rfirst + s);
+            lid = __ldg(a.vid_of + s);
+            const uint2 ab = __ldg(a.ident + s);
+            join_triplet<KEY>(s, ab.x, ab.y, v, n, t);
+        } else if (s < nslots) {
+            first = __ldg(a.sec_first + (s - a.nkey));
+            if (first < a.ncorners) {
+                lid = __ldg(a.vid_of + s);
+                const int32_t* o = a.idx + 3ull * first;
+                v = (uint32_t)__ldg(o);
+                n = (uint32_t)__ldg(o + 1);
+                t = (uint32_t)__ldg(o + 2);
+            }
+        }
+        uint32_t mn[3] = {neutral, neutral, neutral}, mx[3] = {neutral, neutral, neutral};
+        uint32_t bsh = 0xFFFFFFFFu;
+        if (first < a.ncorners) {
+            const uint32_t sh = MULTI ? find_shape(a.shape_off, a.nshapes, first) : 0u;
+            const uint32_t id = lid;
+            if (id < a.vertex_capacity) {
+                const uint32_t lf = a.lastface[id];  // >= 1: the slot's own corners reference the vertex
+                uint32_t k[8];
+                gather_key(a, v, n, t, k);
+                // the winning (highest-numbered) triangle: its gathers are issued before the fingerprint probe so that
+                // both chains are in flight together
+                const uint32_t f = min(max(lf, 1u) - 1u, (a.ncorners - 1) / 3);
+                const uint32_t* sl = a.slot1 + 3ull * f;
+                Tri tr;
+#pragma unroll
+                for (int q = 0; q < 3; ++q) {
+                    uint32_t cv, ct;
+#ifdef VKM_VTX_IDX
+                    cv = (uint32_t)__ldg(a.idx + 9ull * f + 3 * q);
+                    ct = (uint32_t)__ldg(a.idx + 9ull * f + 3 * q + 2);
+#else
+                    corner_v_t<KEY>(a, min(__ldg(sl + q), nslots - 1), 3 * f + q, cv, ct);
+#endif
+                    const float* pp = a.pos + 3ull * min(cv, a.np - 1);
+                    const float2 uu = __ldg(reinterpret_cast<const float2*>(a.uv) + min(ct, a.nt - 1));
+                    tr.px[q] = __ldg(pp); tr.py[q] = __ldg(pp + 1); tr.pz[q] = __ldg(pp + 2);
+                    tr.u[q] = uu.x; tr.v[q] = uu.y;
+                }
+                bool bad = false;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) bad |= nonfinite_bits(k[i]);
+#pragma unroll
+                for (int i = 0; i < 3; ++i)
+                    if ((k[i] & 0x7FFFFFFFu) <= 0x7F800000u) mn[i] = mx[i] = enc_float(__uint_as_float(k[i]));
+                bsh = sh;
+                if (bad) {
+                    a.status->has_unmatchable = 1;
+                } else {
+                    uint32_t kc[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) kc[i] = canon_bits(k[i]);
+                    probe_fingerprint(a, kc, sh);
+                }
+                store_vertex(a.out_vtx + 4ull * id, k, tangent_of(tr));
+            }
+        }
+        // bounding box: one set of (improvement-checked) atomics per warp when its slots share a shape
+        const bool have = (bsh != 0xFFFFFFFFu);
+        const uint32_t any = __ballot_sync(0xFFFFFFFFu, have);
+        if (any) {
+            const uint32_t sh0 = __shfl_sync(0xFFFFFFFFu, bsh, __ffs(any) - 1);
+            if (__all_sync(0xFFFFFFFFu, !have || bsh == sh0)) {
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    mn[i] = __reduce_min_sync(0xFFFFFFFFu, mn[i]);
+                    mx[i] = __reduce_max_sync(0xFFFFFFFFu, mx[i]);
+                }
+                if (lane == 0) box_atomics(a.ext_enc + 6u * sh0, mn, mx);
+            } else if (have) {
+                box_atomics(a.ext_enc + 6u * bsh, mn, mx);
+            }
+        }
+    }
+}
+
+}  // namespace vkm

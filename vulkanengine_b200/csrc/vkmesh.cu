@@ -24,6 +24,7 @@
 #include <vector>
 
 #include "vkm_kernels.cuh"
+#include "vkm_records.cuh"
 #include "vkm_dedup_util.cuh"
 
 using namespace vkm;
@@ -31,6 +32,7 @@ using namespace vkm;
 namespace {
 
 thread_local std::string g_err;
+thread_local vkm_plan_stats g_last_stats{};  // of this thread's last host-entry import
 
 int fail(int code, const char* fmt, ...) {
     char buf[512];
@@ -299,9 +301,17 @@ struct vkm_plan {
     cudaStream_t last_stream = nullptr;
     uint32_t m1 = 0, m2 = 0;       // allocated slots
     uint32_t t1_mode = 0;          // sticky: 0 = locality-preserving triplet table, 1 = scrambled (after clustering)
-    bool assume_clean = false;     // the previous finished import had no value duplicates / NaN-Inf keys
+    bool assume_clean = true;      // speculation for the next import: no value duplicates / NaN-Inf keys (true for nearly
+                                   // every mesh; after a finished import: what that import turned out to be)
     bool force_full = false;       // re-run in progress: launch the complete schedule
     bool ran_full = false;         // what the import in flight was launched with
+    bool ran_records = false;      // the import in flight used the record schedule (vkm_records.cuh)
+    bool records_off = false;      // sticky: the side table would outgrow the slot arrays -> general schedule only
+    uint32_t msec = 0;             // side-table slots of the record schedule
+    uint32_t m2_pct = 200;         // record schedule: value-table slots per 100 key records
+    DevBuf<uint32_t> sec_first;
+    uint32_t seed = 0;             // hash generation (bumped when a table overflows: see hash_triplet)
+    vkm_plan_stats stats{};        // of the import in flight / last finished
     DevBuf<uint32_t> table1, table2;
     DevBuf<uint32_t> slot1, aux1, fbits, fprefix, block_sums, ext_enc, vbase, lastface, out_idx, shape_off;
     DevBuf<float4> out_vtx;
@@ -316,6 +326,7 @@ struct vkm_plan {
     static constexpr int kRing = 32;
     cudaEvent_t ev[kRing][PH_COUNT + 1]{};
     bool ev_used[kRing]{};     // phase events of the slot hold an unharvested measurement
+    int ev_phase[kRing][PH_COUNT]{};  // phase that the interval between event i and i + 1 of the slot belongs to
     bool slot_busy[kRing]{};   // the slot's import may still be running (its end event was recorded)
     uint64_t seq = 0;
     double phase_sum[8]{};
@@ -358,7 +369,7 @@ void plan_harvest(vkm_plan* p, int slot) {
     if (cudaEventSynchronize(p->ev[slot][PH_COUNT]) == cudaSuccess) {
         for (int i = 0; i < PH_COUNT; ++i) {
             float ms = 0.f;
-            if (cudaEventElapsedTime(&ms, p->ev[slot][i], p->ev[slot][i + 1]) == cudaSuccess) p->phase_sum[i] += ms;
+            if (cudaEventElapsedTime(&ms, p->ev[slot][i], p->ev[slot][i + 1]) == cudaSuccess) p->phase_sum[p->ev_phase[slot][i]] += ms;
         }
         p->phase_n++;
     }
@@ -376,11 +387,15 @@ cudaError_t launch_k(bool pdl, void (*kernel)(KArgs...), unsigned grid, unsigned
     cfg.blockDim = dim3(block);
     cfg.dynamicSmemBytes = 0;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int n = 0;
+    if (pdl) {
+        attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n].val.programmaticStreamSerializationAllowed = 1;
+        ++n;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
+    cfg.numAttrs = n;
     return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
@@ -396,6 +411,8 @@ int plan_enqueue(vkm_plan* p) {
     a.aux1 = p->aux1.p;
     a.trip = p->trip.p;
     a.m2 = p->m2;
+    a.seed = p->seed;
+    p->stats.runs++;
     a.cbits = 1;
     while (a.cbits < 32 && (1ull << a.cbits) <= (uint64_t)a.ncorners) a.cbits++;  // 2^cbits > ncorners
     {
@@ -416,19 +433,87 @@ int plan_enqueue(vkm_plan* p) {
         }
     }
     const bool T = p->timing;
-    // Dirty-only kernels (value duplicates, NaN/Inf keys) are not even launched while the plan's previous import
-    // was clean; vkm_plan_finish() checks the status block and re-runs with the full schedule if that was wrong.
+    // Dirty-only kernels (value duplicates, NaN/Inf keys) are not even launched while the plan expects a clean mesh;
+    // vkm_plan_finish() checks the status block and re-runs with the full schedule if that was wrong.
     const bool full = p->force_full || !p->assume_clean;
     p->ran_full = full;
+    // Record schedule (vkm_records.cuh): the clean-mesh speculation with 16-byte key records instead of the hashed table.
+    const uint32_t na_key = std::max(a.np, std::max(a.nn, a.nt));
+    const bool use_rec = !full && !p->records_off && p->t1_mode == 0 && a.ncorners > 0 && (uint64_t)na_key + 8 <= p->table1.n && (uint64_t)na_key / 2 + 2 <= p->trip.n &&
+                         (uint64_t)na_key + p->msec <= p->aux1.n && p->msec > 0;
+    p->ran_records = use_rec;
+    for (int i = 0; i < PH_COUNT; ++i) p->ev_phase[slot][i] = i;
+    cudaError_t le = cudaSuccess;
+    auto L = [&](cudaError_t e) { if (le == cudaSuccess) le = e; };
+    const bool P = !T && a.ncorners < (6u << 20);  // programmatic dependent launch: see below
+    if (use_rec) {
+        a.t1_mode = 0;
+        a.t1_sel = (a.np >= a.nn && a.np >= a.nt) ? 0u : (a.nn >= a.nt ? 1u : 2u);
+        a.rfirst = p->table1.p;                           // (the general schedule's buffers, idle in this one)
+        a.ident = reinterpret_cast<uint2*>(p->trip.p);
+        a.nkey = na_key;
+        a.sec_first = p->sec_first.p;
+        a.msec = p->msec;
+        a.vid_of = p->aux1.p;
+        a.m2 = (uint32_t)std::min<uint64_t>(p->m2, (uint64_t)na_key * p->m2_pct / 100 + 1024) & ~7u;  // whole 8-word buckets
+        const uint32_t nslots = a.nkey + a.msec;
+        const bool multi = a.nshapes > 1;
+        const int key2 = (int)a.t1_sel * 2 + (multi ? 1 : 0);
+        // in time order: clear, insert, flags, scan + ranks, indices, vertices
+        const int order[PH_COUNT] = {PH_CLEAR, PH_INSERT, PH_VALUES, PH_SCAN, PH_INDICES, PH_VERTICES, PH_TANGENTS};
+        for (int i = 0; i < PH_COUNT; ++i) p->ev_phase[slot][i] = order[i];
+        int e = 0;
+        if (T) CU(cudaEventRecord(ev[e++], st));
+        L(launch_k(false, k_clear_records, grid_for(std::max<uint64_t>(a.nkey / 2, a.m2 / 4), kThreads, dev), kThreads, st, a));
+        if (T) CU(cudaEventRecord(ev[e++], st));
+        {
+            const unsigned g1 = grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev, VKM_REC_MINB);  // one resident wave
+#define VKM_K1(K, M) L(launch_k(P, k_insert_records<K, M>, g1, kThreads, st, a))
+            switch (key2) {
+                case 0: VKM_K1(0, false); break;
+                case 1: VKM_K1(0, true); break;
+                case 2: VKM_K1(1, false); break;
+                case 3: VKM_K1(1, true); break;
+                case 4: VKM_K1(2, false); break;
+                default: VKM_K1(2, true); break;
+            }
+#undef VKM_K1
+        }
+        if (T) CU(cudaEventRecord(ev[e++], st));
+        L(launch_k(P, k_flag_records, grid_for(nslots / 4 + 1, kThreads, dev), kThreads, st, a));
+        if (T) CU(cudaEventRecord(ev[e++], st));
+        const uint32_t ntiles = std::max<uint32_t>(1, (a.nwords + kScanTile - 1) / kScanTile);
+        L(launch_k(P, k_scan_tiles, ntiles, kScanThreads, st, a));
+        L(launch_k(P, k_scan_finish, ntiles, kScanThreads, st, a, ntiles, true));
+        L(launch_k(P, k_rank_records, grid_for(nslots / 4 + 1, kThreads, dev), kThreads, st, a));
+        if (T) CU(cudaEventRecord(ev[e++], st));
+        {
+            const unsigned g5 = grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev);
+            if (multi) L(launch_k(P, k_write_indices_rec<true>, g5, kThreads, st, a));
+            else L(launch_k(P, k_write_indices_rec<false>, g5, kThreads, st, a));
+        }
+        if (T) CU(cudaEventRecord(ev[e++], st));
+        {
+            const unsigned g4 = grid_for(nslots, kThreads, dev, VKM_VTX_MINB);
+#define VKM_K4(K, M) L(launch_k(P, k_write_vertices_rec<K, M>, g4, kThreads, st, a))
+            switch (key2) {
+                case 0: VKM_K4(0, false); break;
+                case 1: VKM_K4(0, true); break;
+                case 2: VKM_K4(1, false); break;
+                case 3: VKM_K4(1, true); break;
+                case 4: VKM_K4(2, false); break;
+                default: VKM_K4(2, true); break;
+            }
+#undef VKM_K4
+        }
+        if (T) CU(cudaEventRecord(ev[e++], st));
+    } else {
     if (T) CU(cudaEventRecord(ev[PH_CLEAR], st));
     // Programmatic dependent launch between the kernels of one import (not across the event records of timing mode,
     // and not for k_clear, whose predecessor in the stream is a copy).  Only for imports whose kernels are short:
     // there the launch gaps are a tenth of the import (1 M triangles: 0.121 -> 0.109 ms).  On long kernels it LOSES
     // (16 M triangles: 1.02 -> 1.07 ms): the dependent grid's CTAs move in wherever a slot frees up first, so its
     // 8-per-SM grid-stride split is no longer even and the SMs that took the extra CTAs finish late.
-    const bool P = !T && a.ncorners < (6u << 20);
-    cudaError_t le = cudaSuccess;
-    auto L = [&](cudaError_t e) { if (le == cudaSuccess) le = e; };
     L(launch_k(false, k_clear, grid_for(std::max(a.m1, a.m2) / 4, kThreads, dev), kThreads, st, a));
     if (T) CU(cudaEventRecord(ev[PH_INSERT], st));
     {
@@ -460,7 +545,7 @@ int plan_enqueue(vkm_plan* p) {
     }
     const uint32_t ntiles = std::max<uint32_t>(1, (a.nwords + kScanTile - 1) / kScanTile);
     L(launch_k(P, k_scan_tiles, ntiles, kScanThreads, st, a));
-    L(launch_k(P, k_scan_finish, ntiles, kScanThreads, st, a, ntiles));
+    L(launch_k(P, k_scan_finish, ntiles, kScanThreads, st, a, ntiles, true));
     if (T) CU(cudaEventRecord(ev[PH_INDICES], st));
     if (full) L(launch_k(P, k_final_index, grid_for(a.m1, kThreads, dev), kThreads, st, a));
     L(launch_k(P, k_write_indices, grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, st, a));
@@ -474,6 +559,7 @@ int plan_enqueue(vkm_plan* p) {
                    (const uint32_t*)a.out_idx, (const uint32_t*)a.lastface, (const uint32_t*)&p->status.p->total_vertices,
                    a.vertex_capacity, (const uint32_t*)a.shape_off, (const uint32_t*)a.vbase, a.nshapes, a.vertex_capacity,
                    (const Status*)p->status.p));
+    }
     if (le != cudaSuccess) return fail(VKM_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(le));
     CU(cudaEventRecord(ev[PH_COUNT], st));
     p->slot_busy[slot] = true;
@@ -535,6 +621,11 @@ int vkm_plan_create(const vkm_plan_desc* desc, vkm_plan** out) {
     chk(p->out_idx.ensure(C + 4));
     chk(p->out_vtx.ensure(V * 4));
     chk(p->status.ensure(1));
+    // record schedule: side table for triplets that are not their key record's first variant (grown on overflow)
+    p->msec = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(4096, p->desc.max_attrib / 8), 1u << 30);
+    if (const char* e = getenv("VKM_RECORDS")) p->records_off = atoi(e) == 0;
+    if (const char* e = getenv("VKM_M2_PCT")) p->m2_pct = (uint32_t)std::max(100, atoi(e));
+    chk(p->sec_first.ensure(p->msec));
     if (rc != VKM_OK) {
         vkm_plan_destroy(p);
         return rc;
@@ -563,6 +654,7 @@ void vkm_plan_destroy(vkm_plan* p) {
     p->table1.release(); p->table2.release(); p->slot1.release(); p->aux1.release(); p->fbits.release();
     p->fprefix.release(); p->block_sums.release(); p->ext_enc.release(); p->vbase.release(); p->lastface.release();
     p->out_idx.release(); p->shape_off.release(); p->out_vtx.release(); p->trip.release(); p->status.release();
+    p->sec_first.release();
     if (p->h_status) cudaFreeHost(p->h_status);
     if (p->h_vbase) cudaFreeHost(p->h_vbase);
     if (p->h_ext) cudaFreeHost(p->h_ext);
@@ -575,6 +667,12 @@ void vkm_plan_destroy(vkm_plan* p) {
 
 void vkm_plan_set_timing(vkm_plan* p, int enabled) { if (p) p->timing = enabled != 0; }
 
+int vkm_plan_get_stats(const vkm_plan* p, vkm_plan_stats* out) {
+    if (!p || !out) return fail(VKM_ERR_INVALID_ARG, "vkm_plan_get_stats: null argument");
+    *out = p->stats;
+    return VKM_OK;
+}
+
 int vkm_plan_import(vkm_plan* p, const float* d_pos, uint64_t np, const float* d_nrm, uint64_t nn, const float* d_uv,
                     uint64_t nt, const int32_t* d_idx, const uint64_t* shape_corner_offsets, uint32_t nshapes,
                     void* stream) {
@@ -584,6 +682,8 @@ int vkm_plan_import(vkm_plan* p, const float* d_pos, uint64_t np, const float* d
     const uint64_t C = shape_corner_offsets[nshapes];
     if (C > p->desc.max_corners) return fail(VKM_ERR_CAPACITY, "vkm_plan_import: %llu corners, plan holds %llu", (unsigned long long)C, (unsigned long long)p->desc.max_corners);
     if (np >= 0x7FFFFFFFull || nn >= 0x7FFFFFFFull || nt >= 0x7FFFFFFFull) return fail(VKM_ERR_INVALID_ARG, "vkm_plan_import: attribute arrays beyond the int32 index range");
+    if (((uintptr_t)d_idx & 15) || ((uintptr_t)d_uv & 7) || ((uintptr_t)d_pos & 3) || ((uintptr_t)d_nrm & 3))
+        return fail(VKM_ERR_INVALID_ARG, "vkm_plan_import: d_idx_vnt must be 16-byte, d_uv 8-byte, d_pos/d_nrm 4-byte aligned (vector loads)");
     cudaStream_t st = stream ? (cudaStream_t)stream : p->own_stream;
     if (p->pending && st != p->last_stream) {  // same-stream imports are ordered by the stream itself
         CU(cudaEventSynchronize(p->done));
@@ -618,6 +718,7 @@ int vkm_plan_import(vkm_plan* p, const float* d_pos, uint64_t np, const float* d
     a.vertex_capacity = (uint32_t)std::min<uint64_t>(p->desc.max_vertices, 0xFFFFFFFEull);
     a.status = p->status.p;
     CU(cudaMemcpyAsync(p->shape_off.p, stage, ((uint64_t)nshapes + 1) * 4, cudaMemcpyHostToDevice, st));
+    p->stats = vkm_plan_stats{};
     return plan_enqueue(p);
 }
 
@@ -630,16 +731,50 @@ int vkm_plan_finish(vkm_plan* p, vkm_plan_result* r) {
         p->pending = false;
         const Status s = *p->h_status;
         if (s.bad_index) return fail(VKM_ERR_BAD_INDEX, "import: a vertex/normal/texcoord index is negative or out of range");
+        if (p->ran_records && (s.overflow1 || s.overflow2)) {
+            // record schedule: the side table (seam variants) or the compact fingerprint table was too small -- or
+            // the mesh's keys cluster in this hash generation: grow AND move to the next generation
+            CU(cudaStreamSynchronize(p->last_stream));
+            p->stats.table_overflows++;
+            bool again = attempt <= 16;
+            if (s.overflow1) {
+                const uint64_t cap = p->aux1.n > p->args.nkey ? p->aux1.n - p->args.nkey : 0;  // vid_of holds nkey + msec
+                if (p->msec < cap) {
+                    const uint64_t want = std::min<uint64_t>(cap, 4ull * p->msec);
+                    int rc;
+                    if ((rc = p->sec_first.ensure(want))) return rc;
+                    p->msec = (uint32_t)want;
+                } else {
+                    p->records_off = true;  // more seam variants than key records: the general schedule handles it
+                }
+            }
+            if (s.overflow2) {
+                if (p->args.m2 < (p->m2 & ~7u)) p->m2_pct = 1u << 20;  // use the whole value table from now on
+                else again = false;                                    // fall through to the general growth below
+            }
+            if (again) {
+                p->seed++;
+                p->stats.reseeds++;
+                const int rc = plan_enqueue(p);
+                if (rc) return rc;
+                continue;
+            }
+        }
         if (s.overflow1 || s.overflow2) {
-            // optimistic table sizing failed: grow (bounded by 2 slots per corner) and run the import again
+            // optimistic table sizing failed: grow (bounded by 2 slots per corner) and run the import again.  At the
+            // worst-case size a table is at most half full, so an overflow there means that this mesh's keys cluster in
+            // the current hash generation: every re-run also moves to the next one.
             const uint64_t worst = 2ull * p->args.ncorners + 64;
             CU(cudaStreamSynchronize(p->last_stream));
+            p->stats.table_overflows++;
             int rc = VKM_OK;
-            if (s.overflow1 && p->args.t1_mode == 0 && !s.overflow2) {
+            if (s.overflow1 && p->args.t1_mode == 0 && !s.overflow2 && !p->ran_records) {
                 p->t1_mode = 1;  // the coherent addressing clustered (many triplets per key record): scramble instead
             } else {
-                if ((uint64_t)p->m1 >= worst || attempt > 12) return fail(VKM_ERR_CAPACITY, "import: hash table overflow at worst-case size");
-                rc = plan_size_tables(p, std::min<uint64_t>(worst, 2ull * p->m1));
+                if (attempt > 16) return fail(VKM_ERR_CAPACITY, "import: hash table overflow persists at worst-case size");
+                if ((uint64_t)p->m1 < worst) rc = plan_size_tables(p, std::min<uint64_t>(worst, 2ull * p->m1));
+                p->seed++;
+                p->stats.reseeds++;
             }
             if (rc) return rc;
             if ((rc = plan_enqueue(p))) return rc;
@@ -647,6 +782,7 @@ int vkm_plan_finish(vkm_plan* p, vkm_plan_result* r) {
         }
         const bool dirty = s.has_value_dup || s.has_unmatchable;
         if (dirty && !p->ran_full) {  // the short schedule was launched for a mesh that needs the general path
+            p->stats.mis_speculated = 1;
             p->force_full = true;
             const int rc = plan_enqueue(p);
             p->force_full = false;
@@ -671,6 +807,8 @@ int vkm_plan_finish(vkm_plan* p, vkm_plan_result* r) {
         if (s.capacity_exceeded) return fail(VKM_ERR_CAPACITY, "import: %u unique vertices exceed the plan capacity %llu", s.total_vertices, (unsigned long long)p->desc.max_vertices);
         break;
     }
+    p->stats.schedule = p->ran_records ? 0u : (p->ran_full ? 2u : 1u);
+    p->stats.hash_seed = p->seed;
     const uint32_t S = p->args.nshapes;
     p->vertex_offsets.assign(p->h_vbase, p->h_vbase + S + 1);
     p->extents.resize(S);
@@ -1238,7 +1376,9 @@ static int import_resident(HostCtx& c, const float* d_pos, uint64_t np, const fl
     c.plan->t1_mode = 0;  // every host call is a new mesh: try the coherent addressing first
     if ((rc = vkm_plan_import(c.plan, d_pos, np, d_nrm, nn, d_uv, nt, d_idx, shape_off, nshapes, c.st))) return rc;
     vkm_plan_result r{};
-    if ((rc = vkm_plan_finish(c.plan, &r))) return rc;
+    rc = vkm_plan_finish(c.plan, &r);
+    g_last_stats = c.plan->stats;
+    if (rc) return rc;
     tr.mark("H2D + kernels (finish)");
     const uint64_t vbytes = r.total_vertices * 64, ibytes = C * 4;
     if (g_result_mode.load() == 1) {
@@ -1541,6 +1681,12 @@ int vkm_internal_import_device(int device, const float* d_pos, uint64_t np, cons
     int rc = ctx_bind(c);
     if (rc) return rc;
     return import_resident(c, d_pos, np, d_nrm, nn, d_uv, nt, d_idx, shape_off, nshapes, out, tr);
+}
+
+int vkm_last_import_stats(vkm_plan_stats* out) {
+    if (!out) return fail(VKM_ERR_INVALID_ARG, "vkm_last_import_stats: null argument");
+    *out = g_last_stats;
+    return VKM_OK;
 }
 
 int vkm_set_result_memory(int mode) {
