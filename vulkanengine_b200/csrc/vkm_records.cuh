@@ -88,10 +88,12 @@ __device__ __noinline__ uint32_t insert_side(uint32_t* sec_first, uint32_t msec,
 #define VKM_REC_MINB 4
 #endif
 // Per thread and iteration: 4 consecutive corners = 48 bytes of the index stream = three 128-bit loads.  An
-// iteration costs three memory round trips, not one per corner: (1) the index words (prefetched into L2 four
-// iterations ahead), (2) the slots' first-corner and identity words, all eight loads in flight together, (3) the
-// claims of whichever slots were empty, all issued before the first result is used.  (Measured and dropped: staging
-// the index words through a per-thread cp.async ring in shared memory, 0.28 -> 0.38 ms; 16-byte AoS records.)
+// iteration costs three memory round trips, not one per corner: (1) the index words, (2) the slots' first-corner and
+// identity words, all eight loads in flight together, (3) the claims of whichever slots were empty, all issued before
+// the first result is used.  Measured on B200 and dropped (16.8 M-triangle grid, this kernel 0.277 ms): index words
+// staged through a per-thread cp.async ring in shared memory 0.38 ms; fully coalesced index loads through a
+// warp-private shared-memory transpose 0.317 ms; L1-cached slot loads 0.273 ms (no gain); prefetch.global.L2 of the
+// index words four iterations ahead 0.277 ms (no gain); 16-byte AoS records with a 128-bit CAS 0.43-0.56 ms.
 template <int KEY, bool MULTI>
 __global__ void __launch_bounds__(kThreads, VKM_REC_MINB) k_insert_records(ImportArgs a) {
     pdl_enter();
@@ -117,7 +119,6 @@ __global__ void __launch_bounds__(kThreads, VKM_REC_MINB) k_insert_records(Impor
 #pragma unroll
             for (int i = 0; i < 12; ++i) w[i] = (c0 + i / 3 < a.ncorners) ? __ldg(a.idx + 3ull * c0 + i) : -1;
         }
-        if (g + 4 * stride < g_end) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.idx + 12ull * (g + 4 * stride)));
         uint32_t key[4], oa[4], ob[4], f[4];
         uint2 id[4];
         bool valid[4], tried[4];
@@ -408,12 +409,8 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
 #pragma unroll
                 for (int q = 0; q < 3; ++q) {
                     uint32_t cv, ct;
-#ifdef VKM_VTX_IDX
-                    cv = (uint32_t)__ldg(a.idx + 9ull * f + 3 * q);
-                    ct = (uint32_t)__ldg(a.idx + 9ull * f + 3 * q + 2);
-#else
+                    // (reading (v, vt) straight from the index stream instead: one hop less, 0.40 -> 0.44 ms)
                     corner_v_t<KEY>(a, min(__ldg(sl + q), nslots - 1), 3 * f + q, cv, ct);
-#endif
                     const float* pp = a.pos + 3ull * min(cv, a.np - 1);
                     const float2 uu = __ldg(reinterpret_cast<const float2*>(a.uv) + min(ct, a.nt - 1));
                     tr.px[q] = __ldg(pp); tr.py[q] = __ldg(pp + 1); tr.pz[q] = __ldg(pp + 2);
