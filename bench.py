@@ -32,7 +32,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "mesh triangles/sec (dedup+normals+tangents)"
 UNIT = "triangles/s"
-KERNELS_PER_STEP = 7  # our kernels per clean import (clear, insert, resolve, scan x2, indices, vertices); vkmesh.cu plan_enqueue
+KERNELS_PER_STEP = 8  # our kernels per clean import (clear, insert, flags, scan x2, ranks, indices, vertices); vkmesh.cu plan_enqueue
 FALLBACK_HBM_GBS = 6650.0
 
 WORKLOADS = {
@@ -43,6 +43,8 @@ WORKLOADS = {
     "grid64m": (5793, None, "67.1M-triangle grid (configs[4] base, without injections)"),
     # strong scaling: a FIXED batch of independent meshes, LPT-partitioned over the ranks (configs[3])
     "batch10k": (None, None, "batch of 10k synthetic meshes (1k-100k triangles each, log-uniform), configs[3]"),
+    # config 5: degenerate triangles, duplicated records, +-0 / 1-ulp twins, NaN -- the general (full) schedule
+    "adversarial64m": (5793, None, "67.1M-triangle adversarial mesh (degenerate triangles, duplicated records, +-0 and 1-ulp twins, NaN), configs[4]"),
 }
 
 
@@ -123,62 +125,124 @@ class ClockSampler:
                 "in_timed_region": len(inside) >= 2, "error": self.err}
 
 
-# ------------------------------------------------------------------------------------------ reference arm
-def cpu_reference_run(n: int, repeats: int, threads: int = 1):
-    """Times the reference's own import loop (oracle/_ref, else the plain-C port) on a grid(n) mesh.
-    Returns (triangles per second over all threads, kind)."""
-    from oracle import port, refcpu
+# ------------------------------------------------------------------------------------------ workloads
+def build_workload(args, rank: int = 0, world: int = 1):
+    """The synthetic input of `args.workload` for this rank: (mesh streams, description, scaling)."""
     from vulkanengine_b200 import synth
+
+    n, perm, desc = WORKLOADS[args.workload]
+    if args.workload == "batch10k":
+        from vulkanengine_b200 import sharding
+
+        ns, tris = sharding.batch_sizes(args.batch_meshes)
+        parts = sharding.lpt_partition(tris, world)
+        mesh = sharding.build_shard(ns, parts[rank])
+        desc += f"; {args.batch_meshes} meshes, LPT partition, imbalance {sharding.imbalance(tris, parts):.4f}"
+        return mesh, desc, "strong"
+    if args.workload == "adversarial64m":
+        return synth.adversarial(n, frac=2e-4, nan_frac=2e-5), desc, "weak"
+    # independent meshes per rank: same shape family, different placement
+    mesh = synth.grid(n, permute_seed=perm, offset=(float(rank), -float(rank), 0.5 * rank), scale=1.0 + 0.25 * rank)
+    return mesh, desc, "weak"
+
+
+# ------------------------------------------------------------------------------------------ reference arm
+def host_cores() -> int:
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
+def reference_threads(mesh, want: int) -> int:
+    """Threads for concurrent reference imports of `mesh`: every core, unless memory binds (one import keeps an
+    unordered_map node, a vertex and the result copies per unique vertex: budgeted at 400 B per corner)."""
+    cores = host_cores()
+    t = cores if want <= 0 else min(want, cores)
+    try:
+        avail = os.sysconf("SC_AVPHYS_PAGES") * os.sysconf("SC_PAGE_SIZE")
+        t = min(t, max(1, int(0.6 * avail // max(1, 400 * mesh.corners))))
+    except (ValueError, OSError):
+        pass
+    return max(1, t)
+
+
+def split_shapes(mesh):
+    """A multi-shape stream as a list of independent single-mesh streams (views; the batch10k workload)."""
+    from vulkanengine_b200.synth import MeshStreams
+
+    so = np.asarray(mesh.shape_offsets, np.int64)
+    if len(so) == 2:
+        return [mesh]
+    out = []
+    for s in range(len(so) - 1):
+        ix = mesh.idx[so[s]:so[s + 1]]
+        out.append(MeshStreams(mesh.pos, mesh.nrm, mesh.uv, ix, np.array([0, len(ix)], np.uint64)))
+    return out
+
+
+def cpu_reference_run(mesh, imports: int, threads: int):
+    """Times `imports` passes of the reference's own import loop (oracle/_ref, else the plain-C port) over `mesh` on a
+    pool of `threads` host threads.  The reference imports ONE mesh on ONE thread (MeshLoader::LoadOBJ has no parallel
+    section), so independent imports are the only parallelism its design admits: a pass over a single mesh is one
+    task, a pass over a batch is one task per mesh.  Returns (triangles per second, kind, seconds)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from oracle import port, refcpu
 
     if refcpu.available():
         fn, kind = refcpu.import_arrays, "reference"
     else:
         fn, kind = port.import_arrays, "port"
-    m = synth.grid(n)
+    parts = split_shapes(mesh)
 
-    def work():
-        for _ in range(repeats):
-            fn(m.pos, m.nrm, m.uv, m.idx, m.shape_offsets, collect=False)
+    def work(m):
+        fn(m.pos, m.nrm, m.uv, m.idx, m.shape_offsets, collect=False)  # ctypes releases the GIL
 
     t0 = time.perf_counter()
     if threads <= 1:
-        work()
+        for _ in range(imports):
+            for m in parts:
+                work(m)
     else:
-        ts = [threading.Thread(target=work) for _ in range(threads)]  # ctypes releases the GIL
-        [t.start() for t in ts]
-        [t.join() for t in ts]
+        with ThreadPoolExecutor(threads) as ex:
+            list(ex.map(work, [m for _ in range(imports) for m in parts]))
     dt = time.perf_counter() - t0
-    return m.triangles * repeats * max(threads, 1) / dt, kind, m.triangles, dt
+    return mesh.triangles * imports / dt, kind, dt
 
 
 def run_reference(args, rank, world, emit):
     if rank != 0:
         return
-    # The reference imports one mesh on one thread (MeshLoader::LoadOBJ has no parallel section), so the most host
-    # parallelism its design admits is one independent mesh per core: that is what this arm runs.
-    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    threads = max(1, cores if args.ref_threads <= 0 else min(args.ref_threads, cores))
-    # bounded sample: keep the whole run near two minutes at ~0.5 M triangles/s/thread (all cores busy)
-    budget = 120.0 / max(1, args.steps + args.warmup)
-    tris = int(min(4.2e6, max(2.0e5, 0.5e6 * budget)))
-    n = max(16, int((tris / 2) ** 0.5))
+    # The SAME mesh the GPU arm imports per step (rank 0's), K + W times: a step is one import of it by the reference's
+    # own loop; the imports are independent, so they run on a pool of host threads (as many as cores and memory allow).
+    mesh, desc, scaling = build_workload(args, 0, 1)
+    threads = reference_threads(mesh, args.ref_threads)
+    if len(mesh.shape_offsets) == 2:
+        threads = min(threads, max(args.steps, 1))
     if args.warmup:
-        cpu_reference_run(n, args.warmup, threads)
-    # K timed steps; mesh generation happens before the clock starts inside cpu_reference_run
-    value, kind, ntri, dt = cpu_reference_run(n, args.steps, threads)
-    sample = (f"grid n={n} ({2 * n * n} triangles, same valence-6 family as the GPU workload) per step and per "
-              f"thread; {threads} thread(s), each importing its own mesh concurrently (the reference imports one "
-              f"mesh on one thread; {cores} cores available); g++ -O2 -ffp-contract=off")
+        cpu_reference_run(mesh, args.warmup, min(threads, args.warmup) if len(mesh.shape_offsets) == 2 else threads)
+    value, kind, dt = cpu_reference_run(mesh, args.steps, threads)
+    sample = (f"the workload's own mesh ({mesh.triangles} triangles, {len(mesh.shape_offsets) - 1} mesh(es)), imported "
+              f"{args.steps} times (= steps) by the reference's loop on a pool of {threads} host thread(s) "
+              f"({host_cores()} cores; one import is single-threaded by design); g++ -O2 -ffp-contract=off")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": scaling,
         "vs_baseline": None, "dtype": "u32+f32", "data": "synthetic",
-        "config": {"workload": args.workload, "description": WORKLOADS[args.workload][2], "cpu_sample_grid_n": n},
+        "config": workload_config(args, mesh, desc, None, world),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     emit(line)
+
+
+def workload_config(args, mesh, desc, unique, world):
+    """`config` of the JSON line: identical for both arms (the driver compares them)."""
+    c = {"workload": args.workload, "description": desc, "triangles_per_gpu": mesh.triangles,
+         "corners_per_gpu": mesh.corners, "meshes_per_gpu": len(mesh.shape_offsets) - 1,
+         "parallelism": f"{world} rank(s), independent meshes sharded over GPUs, no collective",
+         "l2": (f"inputs {mesh.input_bytes() / 1e6:.0f} MB per step exceed the 126 MB L2 (no flush needed)"
+                if mesh.input_bytes() > 200e6 else "working set below L2 size: numbers are L2-warm")}
+    return c
 
 
 # ------------------------------------------------------------------------------------------ our arm
@@ -187,7 +251,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--workload", default="highdup16m", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="highdup16m", choices=sorted(WORKLOADS))  # (reference arm: same names)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--e2e-steps", type=int, default=4)
     ap.add_argument("--batch-meshes", type=int, default=10000, help="mesh count of the batch10k workload")
@@ -230,7 +294,6 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = local_rank
     if world > 1:
-        os.environ["NCCL_DEBUG"] = os.environ.get("VKM_NCCL_DEBUG", "WARN")  # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
@@ -253,19 +316,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
-    n, perm, desc = WORKLOADS[args.workload]
-    scaling = "weak"
-    if args.workload == "batch10k":
-        from vulkanengine_b200 import sharding
-
-        scaling = "strong"
-        ns, tris = sharding.batch_sizes(args.batch_meshes)
-        parts = sharding.lpt_partition(tris, world)
-        mesh = sharding.build_shard(ns, parts[rank])
-        desc += f"; {args.batch_meshes} meshes, LPT partition, imbalance {sharding.imbalance(tris, parts):.4f}"
-    else:
-        # independent meshes per rank: same shape family, different placement
-        mesh = synth.grid(n, permute_seed=perm, offset=(float(rank), -float(rank), 0.5 * rank), scale=1.0 + 0.25 * rank)
+    mesh, desc, scaling = build_workload(args, rank, world)
     nshapes = len(mesh.shape_offsets) - 1
     F, C = mesh.triangles, mesh.corners
     max_attrib = max(len(mesh.pos), len(mesh.nrm), len(mesh.uv))
@@ -308,6 +359,42 @@ def main():
     value = total_tris / (ms_total * 1e-3)
     ms_per_step = ms_total / args.steps
 
+    # ---- what a caller gets besides the steady state above (device time, CUDA events around import + finish)
+    def timed_import(pl, arrays, m, reps=1):
+        best = []
+        for _ in range(reps):
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record(stream)
+            pl.import_async(arrays[0].ptr, len(m.pos), arrays[1].ptr, len(m.nrm), arrays[2].ptr, len(m.uv), arrays[3].ptr,
+                            m.shape_offsets, stream=stream.cuda_stream)
+            pl.finish()  # a discarded speculation is re-run in here, on the same stream
+            a1.record(stream)
+            torch.cuda.synchronize()
+            best.append(a0.elapsed_time(a1))
+        return float(np.median(best)), pl.stats()
+
+    schedules = {"steady_state": {"ms": ms_per_step, "stats": plan.stats(),
+                                  "what": "the timed region above: imports queued back to back on a warm plan whose "
+                                          "speculation (clean mesh or not) matches the mesh"}}
+    clean_arrays = (d_pos, d_nrm, d_uv, d_idx)
+    fresh = capi.Plan(dev, C, max_attrib=max_attrib, max_vertices=max_attrib + max_attrib // 8 + 1024, max_shapes=nshapes)
+    ms, st = timed_import(fresh, clean_arrays, mesh)
+    schedules["first_import"] = {"ms": ms, "stats": st, "what": "first import of a newly created plan (cold tables; one import, finish included)"}
+    if nshapes == 1 and not mesh.meta.get("kind") == "adversarial":
+        dirty = synth.with_duplicate_record(mesh)
+        d_dpos = capi.DeviceArray(dev, dirty.pos)
+        d_didx = capi.DeviceArray(dev, dirty.idx)
+        dirty_arrays = (d_dpos, d_nrm, d_uv, d_didx)
+        ms, st = timed_import(fresh, dirty_arrays, dirty)  # the plan expected a clean mesh: record run + full re-run
+        schedules["mis_speculated"] = {"ms": ms, "stats": st, "what": "the same mesh with ONE duplicated position record, after a clean import: the clean-speculating run is discarded and the general schedule runs"}
+        ms, st = timed_import(fresh, dirty_arrays, dirty, reps=5)
+        schedules["full_schedule"] = {"ms": ms, "stats": st, "what": "that not-clean mesh again (the plan now expects it): general schedule only, median of 5"}
+        ms, st = timed_import(fresh, clean_arrays, mesh)
+        schedules["clean_after_dirty"] = {"ms": ms, "stats": st, "what": "the clean mesh after a not-clean one: general schedule (the plan follows the last mesh)"}
+        d_dpos.free()
+        d_didx.free()
+    fresh.destroy()
+
     # ---- roofline
     peak, peak_src = hbm_peak()
     b_alg = mesh.algorithmic_bytes(U)
@@ -315,11 +402,13 @@ def main():
     # algorithmic bytes each phase is the first to read / the one to write (they sum to B_alg)
     # (timed imports run the short schedule: the value-level proof, and with it the first read of the attribute
     # arrays, rides along in the vertex pass; `resolve_values` only sets the flag bits)
+    attr_bytes = mesh.pos.nbytes + mesh.nrm.nbytes + mesh.uv.nbytes + 36 * nshapes  # attributes + extents
+    full = schedules["steady_state"]["stats"].get("schedule") == 2  # general schedule: k_resolve_slots reads the attributes first
     share = {
         "insert_triplets": 36 * F,                                                  # the (v,n,t) index stream
-        "resolve_values": 0,
+        "resolve_values": attr_bytes if full else 0,
         "indices": 12 * F,                                                          # u32 index buffer
-        "vertices": 64 * U + mesh.pos.nbytes + mesh.nrm.nbytes + mesh.uv.nbytes + 36 * nshapes,  # Vertex3D + attributes + extents
+        "vertices": 64 * U + (0 if full else attr_bytes),                           # Vertex3D (+ attributes)
         "tangents": 0, "clear": 0, "mark_scan": 0,
     }
     dom = int(np.argmax(phase_ms[: len(names)]))
@@ -414,6 +503,15 @@ def main():
     pageable_s = max_over_ranks(time.perf_counter() - t0)
     capi.set_result_memory(0)
     barrier()
+    # exactly what integration/engine_shims.cpp does: pageable inputs, malloc()ed results, one synchronous call
+    pageable_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        pageable_step()
+    torch.cuda.synchronize()
+    dropin_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
 
     # The same steps through the batch entry point: every step is one mesh of the batch, its inputs are copied
     # host->device and its results device->host inside the timed region; two lanes per GPU let the copies of one
@@ -459,6 +557,13 @@ def main():
            "api": "vkm_import_batch (host pointers; inputs page-locked; results in the library's recycled page-locked "
                   "blocks, vkm_set_result_memory(1), released with vkm_free_shape inside the timed region; 2 lanes per "
                   "GPU take turns per PCIe direction so one step's upload runs against another step's download)",
+           "needs": "the headline mode asks two things of the engine: page-locked input arrays (vkm_host_alloc; tinyobj's "
+                    "std::vectors are pageable) and vkm_set_result_memory(1) with vkm_free_shape() in ~MeshResource "
+                    "(INTEGRATION.md section 2c); `dropin_default` is the unmodified engine + integration/engine_shims.cpp",
+           "dropin_default": {"value": sum_over_ranks(float(F)) * args.e2e_steps / dropin_s, "unit": UNIT,
+                              "ms_per_step": dropin_s / args.e2e_steps * 1e3,
+                              "api": "vkm_import_shapes, one synchronous call per step, inputs in ordinary pageable memory, "
+                                     "results malloc()ed (what integration/engine_shims.cpp calls; no engine change)"},
            "malloc_results": {"value": sum_over_ranks(float(F)) * nb / malloc_s, "unit": UNIT,
                               "ms_per_step": malloc_s / nb * 1e3,
                               "api": "vkm_import_batch, results malloc()ed per shape as the reference's GeometryConfig "
@@ -476,31 +581,27 @@ def main():
     for p in (h_pos, h_nrm, h_uv, h_idx):
         L.vkm_host_free(p)
 
-    # ---- CPU baseline (rank 0, N = 1 only): the reference's own code on this host, bounded sample
+    # ---- CPU baseline (rank 0, N = 1 only): the reference's own code on this host, on the workload's own mesh
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        ncpu = 1448  # 4.19M triangles per mesh
-        cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-        nthr = max(1, cores if args.ref_threads <= 0 else min(args.ref_threads, cores))
-        v1, kind, ntri, dt1 = cpu_reference_run(ncpu, 1, 1)
-        v, kind, ntri, dt = cpu_reference_run(ncpu, 1, nthr) if nthr > 1 else (v1, kind, ntri, dt1)
+        nthr = reference_threads(mesh, args.ref_threads)
+        single = len(mesh.shape_offsets) == 2
+        v1, kind, dt1 = cpu_reference_run(mesh, 1, 1) if single else (None, None, None)
+        v, kind, dt = cpu_reference_run(mesh, nthr if single else 1, nthr)
         cpu_baseline = {"value": v, "unit": UNIT, "cores": nthr, "kind": kind,
-                        "sample": f"grid n={ncpu} ({ntri} triangles, same family as the workload), one mesh per thread, "
-                                  f"{nthr} threads concurrently, one pass, {dt:.1f} s (the reference imports a mesh on one "
-                                  f"thread, so independent meshes are its only parallelism); g++ -O2 -ffp-contract=off",
-                        "single_thread": {"value": v1, "unit": UNIT, "seconds": dt1}}
+                        "sample": f"the workload's own mesh ({F} triangles, {nshapes} mesh(es)): "
+                                  + (f"{nthr} concurrent imports, one per thread" if single else f"one pass over the batch, one mesh per task on {nthr} threads")
+                                  + f", {dt:.1f} s (the reference imports a mesh on one thread, so independent meshes are its only "
+                                    f"parallelism); g++ -O2 -ffp-contract=off",
+                        "single_thread": ({"value": v1, "unit": UNIT, "seconds": dt1} if single else None)}
 
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "u32+f32", "data": "synthetic",
-            "config": {"workload": args.workload, "description": desc, "triangles_per_gpu": F, "corners_per_gpu": C,
-                       "unique_vertices_per_gpu": U, "meshes_per_gpu": nshapes,
-                       "parallelism": f"{world} rank(s), independent meshes sharded over GPUs, no collective",
-                       "l2": f"inputs {mesh.input_bytes() / 1e6:.0f} MB + outputs {(64 * U + 4 * C) / 1e6:.0f} MB per step exceed the 126 MB L2 (no flush needed)"
-                             if mesh.input_bytes() > 200e6 else "working set below L2 size: numbers are L2-warm"},
-            "roofline": roofline, "pipeline_roofline": pipeline_roofline, "cpu_baseline": cpu_baseline, "e2e": e2e,
+            "config": workload_config(args, mesh, desc, U, world), "unique_vertices_per_gpu": U,
+            "roofline": roofline, "pipeline_roofline": pipeline_roofline, "schedules": schedules, "cpu_baseline": cpu_baseline, "e2e": e2e,
             "gpu_launches": KERNELS_PER_STEP * args.steps, "clocks": clocks,
         }
         emit(line)

@@ -242,6 +242,16 @@ def adversarial(n: int, seed: int = 0x5EED0005, frac: float = 1e-3, nan_frac: fl
                        {"kind": "adversarial", "n": n, "seed": seed})
 
 
+def with_duplicate_record(m: MeshStreams) -> MeshStreams:
+    """The same mesh made "not clean" by ONE duplicated position record: the last corner is redirected to a copy of
+    its own position, so that two distinct (v, n, t) triplets carry one value and must merge.  Unique vertices, indices
+    and sizes stay what they were; only the schedule the importer needs changes (bench.py: full_schedule, mis_speculated)."""
+    pos = np.concatenate([m.pos, m.pos[m.idx[-1, 0]][None, :]])
+    idx = m.idx.copy()
+    idx[-1, 0] = len(pos) - 1
+    return MeshStreams(pos, m.nrm, m.uv, idx, m.shape_offsets, dict(m.meta, duplicate_record=True))
+
+
 def to_obj_text(m: MeshStreams) -> str:
     """OBJ text of a mesh (one `o` per shape), for driving the unmodified reference LoadOBJ in tests.
     Floats are printed with 9 significant digits so that text -> float32 round-trips exactly."""
