@@ -153,12 +153,13 @@ def host_cores() -> int:
 
 def reference_threads(mesh, want: int) -> int:
     """Threads for concurrent reference imports of `mesh`: every core, unless memory binds (one import keeps an
-    unordered_map node, a vertex and the result copies per unique vertex: budgeted at 400 B per corner)."""
+    unordered_map node, a vector element and the result copies per unique vertex: about 50 B per corner on the grid
+    family, budgeted at 100 B)."""
     cores = host_cores()
     t = cores if want <= 0 else min(want, cores)
     try:
         avail = os.sysconf("SC_AVPHYS_PAGES") * os.sysconf("SC_PAGE_SIZE")
-        t = min(t, max(1, int(0.6 * avail // max(1, 400 * mesh.corners))))
+        t = min(t, max(1, int(0.6 * avail // max(1, 100 * mesh.corners))))
     except (ValueError, OSError):
         pass
     return max(1, t)
