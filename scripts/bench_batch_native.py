@@ -14,6 +14,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--meshes", type=int, default=2000)
 ap.add_argument("--result-memory", type=int, default=1)
 ap.add_argument("--repeats", type=int, default=3)
+ap.add_argument("--gpus", type=int, default=1, help="GPUs of this ONE process (vkm_init([0..N-1]); the batch is LPT-partitioned over them)")
 args = ap.parse_args()
 
 meshes = synth.batch(args.meshes)
@@ -29,6 +30,7 @@ for i, m in enumerate(meshes):
     ins[i] = capi.MeshIn(m.pos.ctypes.data, len(m.pos), m.nrm.ctypes.data, len(m.nrm), m.uv.ctypes.data, len(m.uv),
                          m.idx.ctypes.data, so.ctypes.data, len(so) - 1)
     outs[i] = C.cast(arr, C.POINTER(capi.ShapeOut))
+capi.init(list(range(args.gpus)))
 capi.set_result_memory(args.result_memory)
 F = sum(m.triangles for m in meshes)
 bytes_in = sum(m.input_bytes() for m in meshes)
@@ -43,6 +45,6 @@ for r in range(args.repeats + 1):
         L.vkm_free_shape(C.byref(outs[i][0]))
     if r:
         best = min(best, dt)
-print(json.dumps({"meshes": n, "triangles": F, "unique_vertices": nv, "input_MB": bytes_in / 1e6,
+print(json.dumps({"gpus": args.gpus, "meshes": n, "triangles": F, "unique_vertices": nv, "input_MB": bytes_in / 1e6,
                   "output_MB": (64 * nv + 12 * F) / 1e6, "result_memory": args.result_memory, "seconds": best,
                   "triangles_per_s": F / best, "us_per_mesh": best / n * 1e6}))
