@@ -18,6 +18,7 @@
 
 #include "resources/geometry/geometry.hpp"
 #include "systems/geometry/geometry_system.hpp"
+#include "core/utils/freelist.hpp"
 #include "systems/resource/loaders/mesh/mesh_loader.hpp"
 #include "systems/resource/resources/mesh/mesh_resource.hpp"
 #include "vendor/tinyobj/tinyobj.hpp"
@@ -211,6 +212,16 @@ void ref_generate_cube(float width, float height, float depth, float tile_x, flo
     Engine::GeometryConfig c = fake_geometry_system()->GenerateCubeConfig(width, height, depth, tile_x, tile_y, "c", "m");
     hand_over(c, vc, ic, v, idx);
 }
+
+// ---------------- Freelist (core/utils/freelist.cpp): the first-fit allocator behind the renderer's buffers ----------------
+void* ref_freelist_create(uint64_t total) { return new Engine::Freelist(total); }
+void ref_freelist_destroy(void* f) { delete (Engine::Freelist*)f; }
+uint64_t ref_freelist_alloc(void* f, uint64_t size) {  // Freelist::AllocateBlock (:144-164): offset, or UINT64_MAX
+    Engine::FreelistNode* n = ((Engine::Freelist*)f)->AllocateBlock(size);
+    return n ? n->GetMemoryOffset() : UINT64_MAX;
+}
+int ref_freelist_free(void* f, uint64_t offset) { return ((Engine::Freelist*)f)->FreeByOffset(offset) ? 1 : 0; }
+uint64_t ref_freelist_free_space(void* f) { return ((Engine::Freelist*)f)->FreeSpace(); }
 
 // ---------------- std::hash<Vertex3D> / operator== (renderer_types.hpp:20-27,72-86) ----------------
 uint64_t ref_hash_vertex(const void* v64) { return std::hash<Engine::Vertex3D>()(*(const Engine::Vertex3D*)v64); }

@@ -254,3 +254,35 @@ def generate_cube(width, height, depth, tile_x, tile_y):
     vc, ic, vp, ip = C.c_uint32(), C.c_uint32(), C.c_void_p(), C.c_void_p()
     lib().ref_generate_cube(width, height, depth, tile_x, tile_y, C.byref(vc), C.byref(ic), C.byref(vp), C.byref(ip))
     return _take(vc, ic, vp, ip)
+
+
+class Freelist:
+    """The reference's own first-fit allocator (core/utils/freelist.cpp) behind ctypes.  NOTE: its FreeBlock merges
+    neighbours with dangling pointers (freelist.cpp:36-72); only allocation-only and last-in-first-out release
+    sequences are safe to run (random release orders crash inside FreeByOffset after a few dozen steps)."""
+
+    def __init__(self, total: int):
+        L = lib()
+        L.ref_freelist_create.restype = C.c_void_p
+        L.ref_freelist_create.argtypes = [C.c_uint64]
+        L.ref_freelist_destroy.argtypes = [C.c_void_p]
+        L.ref_freelist_alloc.restype = C.c_uint64
+        L.ref_freelist_alloc.argtypes = [C.c_void_p, C.c_uint64]
+        L.ref_freelist_free.argtypes = [C.c_void_p, C.c_uint64]
+        L.ref_freelist_free_space.restype = C.c_uint64
+        L.ref_freelist_free_space.argtypes = [C.c_void_p]
+        self.L, self.h = L, L.ref_freelist_create(total)
+
+    def alloc(self, size: int) -> int:
+        return int(self.L.ref_freelist_alloc(self.h, size))
+
+    def free(self, offset: int) -> bool:
+        return bool(self.L.ref_freelist_free(self.h, offset))
+
+    def free_space(self) -> int:
+        return int(self.L.ref_freelist_free_space(self.h))
+
+    def close(self):
+        if self.h:
+            self.L.ref_freelist_destroy(self.h)
+            self.h = None

@@ -1,7 +1,15 @@
-"""CPU test of the first-fit range allocator behind the headless renderer handoff.  The
-expected offsets come from a direct restatement of the reference's Freelist (core/utils/freelist.cpp:144-159:
-walk the node list from the lowest offset, take the first free node that fits, split it)."""
+"""CPU test of the first-fit range allocator behind the headless renderer handoff.
+
+Pinned to the reference's OWN allocator (Freelist::AllocateBlock / FreeByOffset / FreeSpace, core/utils/freelist.cpp,
+compiled unmodified into oracle/_ref) on the sequences it can run: allocation only -- all the engine ever does,
+FreeDataRange is a no-op (vulkan.cpp:29-31) -- and last-in-first-out releases.  The reference's FreeBlock
+(freelist.cpp:36-72) merges neighbours through dangling pointers: with releases in any other order it crashes inside
+FreeByOffset after a few dozen steps (observed here), so random release orders are checked against a plain first-fit
+model instead (walk from the lowest offset, take the first free range that fits, split it; merge on release)."""
 import numpy as np
+import pytest
+
+from oracle import refcpu
 
 from vulkanengine_b200 import capi
 
@@ -33,7 +41,7 @@ class FirstFit:  # restatement of Freelist::AllocateBlock / FreeBlock on a sorte
         self.free = merged
 
 
-def test_first_fit_sequence_matches_reference_freelist():
+def test_random_release_order_matches_a_first_fit_model():
     L = capi.lib()
     total = 64 << 20  # the engine's global vertex buffer size (vulkan.cpp:599-628)
     a = L.vkm_rangealloc_create(total)
@@ -56,6 +64,37 @@ def test_first_fit_sequence_matches_reference_freelist():
     off, size = live[0]
     assert L.vkm_rangealloc_free(a, off, size) == 0
     assert L.vkm_rangealloc_free(a, off, size) != 0
+    L.vkm_rangealloc_destroy(a)
+
+
+@pytest.mark.skipif(not refcpu.available(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("lifo", [False, True], ids=["alloc_only", "lifo_release"])
+def test_offsets_and_free_space_equal_the_reference_freelist(lifo):
+    L = capi.lib()
+    total = 64 << 20
+    a = L.vkm_rangealloc_create(total)
+    ref = refcpu.Freelist(total)
+    rng = np.random.default_rng(7)
+    live = []
+    for step in range(3000):
+        if lifo and live and rng.random() < 0.4:
+            off, size = live.pop()
+            assert L.vkm_rangealloc_free(a, off, size) == 0
+            assert ref.free(off)
+        else:
+            size = int(rng.integers(1, 200_000 if lifo else 800)) * 64
+            if L.vkm_rangealloc_free_space(a) < size:  # (the reference logs through its Logger singleton when it is full)
+                continue
+            got, want = L.vkm_rangealloc_alloc(a, size), ref.alloc(size)
+            assert got == want, (step, got, want)
+            live.append((got, size))
+        assert L.vkm_rangealloc_free_space(a) == ref.free_space()
+    # exact fit of what is left, as the reference does it
+    rest = ref.free_space()
+    if rest:
+        assert L.vkm_rangealloc_alloc(a, rest) == ref.alloc(rest)
+        assert L.vkm_rangealloc_free_space(a) == ref.free_space() == 0
+    ref.close()
     L.vkm_rangealloc_destroy(a)
 
 
