@@ -132,13 +132,15 @@ typedef struct vkm_mesh_in {
 } vkm_mesh_in;
 int vkm_import_batch(const vkm_mesh_in* meshes, uint32_t count, vkm_shape_out* const* outs, int* statuses);
 
-/* ---- OBJ text -> tinyobj-shaped streams on the GPU.  Replaces, for `v`/`vn`/`vt` records, triangle and quad
- *      faces, `o`/`g` shapes and `usemtl`, the call tinyobj::LoadObj(&attributes, &shapes, &materials, ...) in
- *      MeshLoader::LoadOBJ (mesh_loader.cpp:219; parser tinyobj.hpp:2557-3115) -- same floats (the parser's own
- *      decimal routine is reproduced), same index_t streams, same shape split and names.  Polygons with more than
- *      four corners and l / p / vw / t records return VKM_ERR_UNSUPPORTED: the caller keeps its CPU parser for
- *      those files.  .mtl files are not read: `usemtl_names[i]` is the name in force at shape i's first face (the
- *      engine uses material_ids[0], mesh_loader.cpp:231) for the caller to look up. ---- */
+/* ---- OBJ text -> tinyobj-shaped streams on the GPU.  Replaces the call tinyobj::LoadObj(&attributes, &shapes,
+ *      &materials, ...) in MeshLoader::LoadOBJ (mesh_loader.cpp:219; parser tinyobj.hpp:2557-3115) for `v`/`vn`/`vt`
+ *      records, faces of 3 to 255 corners (quads by the shorter diagonal, larger polygons by the parser's own ear
+ *      clipping, tinyobj.hpp:1714-1935), `o`/`g` shapes, `usemtl` and `mtllib` -- same floats (the parser's decimal
+ *      routine is reproduced), same index_t streams in the same triangle order, same shape split, names and
+ *      material names.  VKM_ERR_UNSUPPORTED is left for l / p / vw / t records, polygons beyond 255 corners and
+ *      quads / polygons that name a vertex beyond the file's `v` records (tinyobj's treatment of those depends on
+ *      where in the file the record appears); a zero or unresolvable index is VKM_ERR_BAD_INDEX (tinyobj fails the
+ *      load). ---- */
 typedef struct vkm_obj_streams {
     float* pos;   uint64_t np;  /* attrib_t::vertices  (malloc) */
     float* nrm;   uint64_t nn;  /* attrib_t::normals */
@@ -147,9 +149,20 @@ typedef struct vkm_obj_streams {
     uint64_t* shape_corner_offsets; /* nshapes + 1 */
     uint32_t nshapes;
     char** shape_names;         /* shape_t::name */
-    char** usemtl_names;
+    char** usemtl_names;        /* the raw `usemtl` name in force at the shape's first face */
+    char** material_names;      /* materials[shape.mesh.material_ids[0]].name, "" when the id is -1: what
+                                   mesh_loader.cpp:231, 312-314 put into GeometryConfig::material_name */
 } vkm_obj_streams;
-int vkm_parse_obj(int device, const char* text, uint64_t len, vkm_obj_streams* out);
+/* A material file the OBJ text may name on a `mtllib` line (the text entry points do not touch the file system:
+ * the caller reads the .mtl it finds next to the .obj, as tinyobj's MaterialFileReader would, tinyobj.hpp:2442-2480). */
+typedef struct vkm_mtl_source {
+    const char* filename;  /* as written after `mtllib`, e.g. "falcon.mtl" */
+    const char* text;
+    uint64_t len;
+} vkm_mtl_source;
+int vkm_parse_obj(int device, const char* text, uint64_t len, vkm_obj_streams* out);  /* no .mtl: material_names all "" */
+int vkm_parse_obj_mtl(int device, const char* text, uint64_t len, const vkm_mtl_source* mtls, uint32_t nmtl,
+                      vkm_obj_streams* out);
 void vkm_free_obj_streams(vkm_obj_streams* streams);
 
 /* The whole of MeshLoader::LoadOBJ (mesh_loader.cpp:200-328) from OBJ text: parse on the GPU, run the geometry
@@ -160,8 +173,11 @@ typedef struct vkm_obj_import {
     vkm_shape_out* shapes;
     char** shape_names;
     char** usemtl_names;
+    char** material_names;      /* GeometryConfig::material_name (see vkm_obj_streams) */
 } vkm_obj_import;
 int vkm_import_obj_text(int device, const char* text, uint64_t len, vkm_obj_import* out);
+int vkm_import_obj_text_mtl(int device, const char* text, uint64_t len, const vkm_mtl_source* mtls, uint32_t nmtl,
+                            vkm_obj_import* out);
 void vkm_free_obj_import(vkm_obj_import* result);
 
 /* ---- E3DM import cache: replaces b8 MeshLoader::WriteToE3DM(const std::string&, const std::string&,

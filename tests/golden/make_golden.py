@@ -11,6 +11,8 @@ oracle/Makefile) exist.  The fixtures travel to the GPU box; the reference tree 
                    outputs: reference LoadOBJ run here (no golden is shipped for this asset).
   cube.npz         the 24-vertex / 36-index cube of GeometrySystem::GenerateCubeConfig
                    (geometry_system.cpp:296-439) after the reference's GenerateNormals + GenerateTangents.
+  asset_text.npz   the bytes of falcon.obj / falcon.mtl / viking_room.obj themselves (reference assets; viking_room's
+                   .mtl is not shipped), so that the GPU box can run OBJ TEXT -> E3DM without the reference tree.
   semantics.npz    tiny hand-built edge cases (NaN keys, +-0 twins, 1-ulp twins, degenerate triangles)
                    through the reference import loop.
 """
@@ -112,9 +114,18 @@ def semantics():
     np.savez_compressed(os.path.join(HERE, "semantics.npz"), **out)
 
 
+def asset_text():
+    out = {}
+    for f in ("falcon.obj", "falcon.mtl", "viking_room.obj"):
+        out[f.replace(".", "_")] = np.frombuffer(open(MODELS + f, "rb").read(), np.uint8)
+    np.savez_compressed(os.path.join(HERE, "asset_text.npz"), **out)
+    print("asset_text", {k: len(v) for k, v in out.items()})
+
+
 if __name__ == "__main__":
     assert refcpu.available(), "build oracle/_ref first: make -C oracle ref"
     asset("falcon", MODELS + "falcon.e3dm")
     asset("viking_room")
     cube()
     semantics()
+    asset_text()

@@ -28,7 +28,7 @@ SYMBOLS = [
     "vkm_generate_tangents", "vkm_generate_normals", "vkm_deduplicate_vertices",
     "vkm_import_shapes", "vkm_free_shape", "vkm_set_result_memory", "vkm_host_alloc", "vkm_host_free", "vkm_import_batch",
     "vkm_e3dm_write", "vkm_e3dm_read", "vkm_e3dm_free", "vkm_parse_obj", "vkm_free_obj_streams",
-    "vkm_import_obj_text", "vkm_free_obj_import", "vkm_generate_plane_config", "vkm_generate_cube_config",
+    "vkm_import_obj_text", "vkm_free_obj_import", "vkm_parse_obj_mtl", "vkm_import_obj_text_mtl", "vkm_generate_plane_config", "vkm_generate_cube_config",
     "vkm_plan_create", "vkm_plan_destroy", "vkm_plan_import", "vkm_plan_finish", "vkm_plan_set_timing",
     "vkm_plan_phase_name", "vkm_plan_get_stats", "vkm_last_import_stats", "vkm_generate_tangents_dev", "vkm_generate_normals_dev",
     "vkm_generate_tangents_dev_noalloc",
@@ -68,12 +68,17 @@ class ObjStreams(C.Structure):
     _fields_ = [("pos", C.POINTER(C.c_float)), ("np", C.c_uint64), ("nrm", C.POINTER(C.c_float)), ("nn", C.c_uint64),
                 ("uv", C.POINTER(C.c_float)), ("nt", C.c_uint64), ("idx_vnt", C.POINTER(C.c_int32)),
                 ("shape_corner_offsets", C.POINTER(C.c_uint64)), ("nshapes", C.c_uint32),
-                ("shape_names", C.POINTER(C.c_char_p)), ("usemtl_names", C.POINTER(C.c_char_p))]
+                ("shape_names", C.POINTER(C.c_char_p)), ("usemtl_names", C.POINTER(C.c_char_p)),
+                ("material_names", C.POINTER(C.c_char_p))]
 
 
 class ObjImport(C.Structure):
     _fields_ = [("nshapes", C.c_uint32), ("shapes", C.POINTER(ShapeOut)), ("shape_names", C.POINTER(C.c_char_p)),
-                ("usemtl_names", C.POINTER(C.c_char_p))]
+                ("usemtl_names", C.POINTER(C.c_char_p)), ("material_names", C.POINTER(C.c_char_p))]
+
+
+class MtlSource(C.Structure):
+    _fields_ = [("filename", C.c_char_p), ("text", C.c_char_p), ("len", C.c_uint64)]
 
 
 class PoolGeometry(C.Structure):
@@ -329,13 +334,27 @@ class ParsedObj:
     shape_offsets: np.ndarray
     shape_names: list
     usemtl_names: list
+    material_names: list = None  # GeometryConfig::material_name per shape ("" when the usemtl resolved to no material)
 
 
-def parse_obj(text: bytes, device: int = 0) -> ParsedObj:
-    """vkm_parse_obj: OBJ text -> tinyobj-shaped streams, parsed on the GPU."""
+def _mtl_array(mtls):
+    """{filename: text bytes} -> (MtlSource array, count, keep-alive list)."""
+    items = list((mtls or {}).items())
+    arr = (MtlSource * max(1, len(items)))()
+    keep = []
+    for i, (name, text) in enumerate(items):
+        nb = name.encode() if isinstance(name, str) else name
+        keep += [nb, text]
+        arr[i] = MtlSource(nb, text, len(text))
+    return arr, len(items), keep
+
+
+def parse_obj(text: bytes, device: int = 0, mtls: dict | None = None) -> ParsedObj:
+    """vkm_parse_obj[_mtl]: OBJ text (+ the .mtl texts it may name) -> tinyobj-shaped streams, parsed on the GPU."""
     L = lib()
     s = ObjStreams()
-    _check(L.vkm_parse_obj(device, text, len(text), C.byref(s)))
+    arr, n, _keep = _mtl_array(mtls)
+    _check(L.vkm_parse_obj_mtl(device, text, len(text), arr, n, C.byref(s)))
     try:
         ns = s.nshapes
         ncorners = int(s.shape_corner_offsets[ns]) if ns else 0
@@ -347,16 +366,19 @@ def parse_obj(text: bytes, device: int = 0) -> ParsedObj:
         so = np.array([s.shape_corner_offsets[i] for i in range(ns + 1)], np.uint64)
         names = [s.shape_names[i].decode() for i in range(ns)]
         mats = [s.usemtl_names[i].decode() for i in range(ns)]
-        return ParsedObj(pos, nrm, uv, idx, so, names, mats)
+        return ParsedObj(pos, nrm, uv, idx, so, names, mats, [s.material_names[i].decode() for i in range(ns)])
     finally:
         L.vkm_free_obj_streams(C.byref(s))
 
 
-def import_obj_text(text: bytes, device: int = 0):
-    """vkm_import_obj_text: OBJ text -> finished shapes, all on the GPU.  Returns (shapes, names, usemtl names)."""
+def import_obj_text(text: bytes, device: int = 0, mtls: dict | None = None):
+    """vkm_import_obj_text[_mtl]: OBJ text -> finished shapes, all on the GPU.  Returns (shapes, names, material names):
+    with `mtls` ({filename: bytes}) the material names are GeometryConfig::material_name as the engine derives it,
+    without it the raw usemtl names (the entry point without .mtl sources resolves every material to "")."""
     L = lib()
     r = ObjImport()
-    _check(L.vkm_import_obj_text(device, text, len(text), C.byref(r)))
+    arr, n, _keep = _mtl_array(mtls)
+    _check(L.vkm_import_obj_text_mtl(device, text, len(text), arr, n, C.byref(r)))
     try:
         shapes, names, mats = [], [], []
         for i in range(r.nshapes):
@@ -365,7 +387,7 @@ def import_obj_text(text: bytes, device: int = 0):
             shapes.append(ShapeResult(_copy_out(o.vertices, 64 * o.vertex_count, VERTEX_DTYPE),
                                       _copy_out(o.indices, 4 * o.index_count, np.uint32), e))
             names.append(r.shape_names[i].decode())
-            mats.append(r.usemtl_names[i].decode())
+            mats.append((r.material_names[i] if mtls is not None else r.usemtl_names[i]).decode())
         return shapes, names, mats
     finally:
         L.vkm_free_obj_import(C.byref(r))
