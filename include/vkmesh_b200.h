@@ -333,6 +333,7 @@ int vkm_dev_free(int device, void* d_ptr);
 int vkm_dev_upload(int device, void* d_dst, const void* h_src, uint64_t bytes);
 int vkm_dev_download(int device, void* h_dst, const void* d_src, uint64_t bytes);
 int vkm_dev_sync(int device);
+int vkm_dev_mem_info(int device, uint64_t* free_bytes, uint64_t* total_bytes);  /* cudaMemGetInfo */
 
 #ifdef __cplusplus
 }

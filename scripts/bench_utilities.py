@@ -81,6 +81,56 @@ for name, f, useful, floor in (
                  "sector_floor_bytes": floor, "frac_sector_floor": floor / (ms * 1e-3) / 1e9 / peak,
                  "launches_per_call": "1 memset + 2 kernels"}
 
+# ---- the same utilities through the HOST entry points (what the engine's Geometry:: statics call): caller arrays in
+# pageable memory, upload + kernels + download of the changed column inside the timed region
+shapes_h = plan.fetch(r, m.shape_offsets)
+hv, hi = shapes_h[0].vertices.copy(), np.ascontiguousarray(shapes_h[0].indices)
+capi.init([dev])
+
+
+def host_timed(fn, reps=3):
+    fn()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        fn()
+    return (time.perf_counter() - t0) / reps * 1e3
+
+
+for name, f in (("generate_tangents", L.vkm_generate_tangents), ("generate_normals", L.vkm_generate_normals)):
+    ms = host_timed(lambda: capi._check(f(len(hv), hv.ctypes.data, len(hi), hi.ctypes.data)))
+    out[name]["host_e2e"] = {"ms": ms, "triangles_per_s": F / (ms * 1e-3), "h2d_bytes": int(hv.nbytes + hi.nbytes),
+                             "d2h_bytes": int(len(hv) * (16 if name == "generate_tangents" else 12)),
+                             "api": "vkm_" + name + " (pageable caller arrays; only the changed column is downloaded)"}
+# Geometry::DeduplicateVertices: the first 2^20 corners of the mesh expanded to one vertex per corner (about 6 copies
+# of every vertex), indices 0 .. n-1
+nd = min(1 << 20, C)
+dv = np.ascontiguousarray(hv[hi[:nd]])
+di = np.arange(nd, dtype=np.uint32)
+
+
+def dedup_once():
+    ix = di.copy()
+    outp = C_.c_void_p()
+    n_u = L.vkm_deduplicate_vertices(nd, dv.ctypes.data, nd, ix.ctypes.data, C_.byref(outp))
+    assert n_u != 0xFFFFFFFF, L.vkm_last_error()
+    C_.CDLL(None).free(outp)
+    return n_u
+
+
+import ctypes as C_  # noqa: E402
+
+n_unique = dedup_once()
+ms = host_timed(dedup_once)
+out["deduplicate_vertices"] = {"ms": ms, "vertices_in": nd, "vertices_out": int(n_unique), "vertices_per_s": nd / (ms * 1e-3),
+                               "api": "vkm_deduplicate_vertices (host arrays in and out; cell hash + one-warp recurrence + remap)"}
+nsmall = 20000  # the reference's loop is O(V * U): a bounded sample
+if refcpu.available():
+    sv, si = np.ascontiguousarray(dv[:nsmall]), np.arange(nsmall, dtype=np.uint32)
+    t0 = time.perf_counter()
+    refcpu.deduplicate_vertices(sv, si)
+    out["deduplicate_vertices"]["cpu_reference"] = {"vertices_in": nsmall, "seconds": time.perf_counter() - t0,
+                                                    "note": "Geometry::DeduplicateVertices is quadratic; 1 thread"}
+
 # the reference's own functions on this host (1 thread: they are plain loops), bounded sample
 mc = synth.grid(args.cpu_grid)
 shapes = port.import_arrays(mc.pos, mc.nrm, mc.uv, mc.idx, mc.shape_offsets)

@@ -60,3 +60,27 @@ def test_no_cpu_fallback_without_device():
     with pytest.raises(capi.VkmError) as e:
         capi.Plan(0, 3)
     assert e.value.code == 5
+
+
+def test_obj_number_parser_has_no_fused_multiply_add():
+    """The decimal routine must round every product and sum separately, as the CPU parser does (built without
+    contraction): the SASS of the record-parsing kernel may not contain DFMA."""
+    import shutil
+    import subprocess
+
+    from vulkanengine_b200 import build
+
+    if not shutil.which("cuobjdump"):
+        import pytest
+
+        pytest.skip("cuobjdump not on PATH")
+    sass = subprocess.run(["cuobjdump", "-sass", build.LIB_PATH], capture_output=True, text=True).stdout
+    fn, hits, seen = None, 0, False
+    for line in sass.splitlines():
+        if "Function :" in line:
+            fn = line.split("Function :")[1].strip()
+            seen |= "k_parse_records" in fn
+        elif fn and "k_parse_records" in fn and "DFMA" in line:
+            hits += 1
+    assert seen, "k_parse_records not found in the library's SASS"
+    assert hits == 0, f"{hits} DFMA instructions in k_parse_records"

@@ -269,3 +269,23 @@ def test_cached_parser_state_across_sizes_and_shutdown(tmp_path):
     from oracle import port
     from conftest import assert_shapes_equal
     assert_shapes_equal(got, port.import_arrays(m.pos, m.nrm, m.uv, m.idx, m.shape_offsets))
+
+
+def test_decimal_fuzz_matches_tinyobj_bit_for_bit(tmp_path):
+    """60 000 random decimal literals (many digits, long fractions, exponents): every float equal to tinyobj's.  A fused
+    multiply-add anywhere in the accumulation shows up here as a float that is 1 ulp off."""
+    rng = np.random.default_rng(2024)
+    lines = []
+    for _ in range(20000):
+        parts = []
+        for _ in range(3):
+            nd = int(rng.integers(1, 30))
+            digs = "".join(str(int(d)) for d in rng.integers(0, 10, nd))
+            dot = int(rng.integers(0, nd + 1))
+            s = (digs[:dot] + "." + digs[dot:]) if rng.random() < 0.85 else digs
+            if rng.random() < 0.35:
+                s += ("e" if rng.random() < 0.5 else "E") + ("+" if rng.random() < 0.2 else "") + str(int(rng.integers(-60, 50)))
+            parts.append(("-" if rng.random() < 0.3 else "") + s)
+        lines.append("v " + " ".join(parts))
+    lines.append("f 1 2 3")
+    compare("\n".join(lines) + "\n", tmp_path, "fuzz")

@@ -10,6 +10,11 @@ What is checked, through the C ABI only:
     bit -- the tolerance the other parity tests use: 0 ULP, NaN equal to NaN -- on two calls in a row, the
     second on a different and smaller mesh, so that words left in the shared array by the first call
     would show up as wrong tangents;
+  * the same output equals the CPU oracle's GenerateTangents (the reference's own function where oracle/_ref is
+    present), so that the comparison does not rest on two CUDA paths agreeing with each other;
+  * a mesh of exactly VKM_NOALLOC_MAX_VERTICES vertices, the largest the built-in array takes, comes out right;
+  * the call really allocates nothing: the device's free memory (cudaMemGetInfo) is the same before and after a
+    series of calls;
   * sizes beyond VKM_NOALLOC_MAX_VERTICES are refused with VKM_ERR_CAPACITY and a message that says so.
 """
 import ctypes as C
@@ -60,6 +65,62 @@ def test_noalloc_tangents_match_existing_entry_point_twice_in_a_row():
         ok, msg = vertices_equal(b, a)
         assert ok, msg
         assert not np.array_equal(a["tangent"].view(np.uint32), v["tangent"].view(np.uint32))  # something was computed
+
+
+def _oracle_tangents(v, idx):
+    from oracle import port, refcpu
+
+    w = v.copy()
+    (refcpu.generate_tangents if refcpu.available() else port.generate_tangents)(w, idx.copy())
+    return w
+
+
+def _noalloc(v, idx, repeats=1):
+    L = capi.lib()
+    d_v = capi.DeviceArray(0, v)
+    d_i = capi.DeviceArray(0, idx)
+    for _ in range(repeats):
+        capi._check(L.vkm_generate_tangents_dev_noalloc(len(v), d_v.ptr, len(idx), d_i.ptr, None))
+    capi._check(L.vkm_dev_sync(0))
+    out = d_v.download(capi.VERTEX_DTYPE)
+    d_v.free()
+    d_i.free()
+    return out
+
+
+def test_noalloc_tangents_equal_the_cpu_oracle():
+    for mesh in (synth.grid(150), synth.adversarial(60), synth.uv_sphere(20, 40)):
+        v, idx = _mesh_buffers(mesh)
+        ok, msg = vertices_equal(_noalloc(v, idx), _oracle_tangents(v, idx))
+        assert ok, msg
+
+
+def test_noalloc_at_exactly_the_maximum_vertex_count():
+    n = 1023  # (n + 1)^2 = 1024^2 = VKM_NOALLOC_MAX_VERTICES unique vertices
+    m = synth.grid(n)
+    v, idx = _mesh_buffers(m)
+    assert len(v) == MAX_VERTICES
+    ok, msg = vertices_equal(_noalloc(v, idx), _oracle_tangents(v, idx))
+    assert ok, msg
+
+
+def test_noalloc_calls_leave_the_free_device_memory_unchanged():
+    L = capi.lib()
+    v, idx = _mesh_buffers(synth.grid(200))
+    d_v = capi.DeviceArray(0, v)
+    d_i = capi.DeviceArray(0, idx)
+    capi._check(L.vkm_generate_tangents_dev_noalloc(len(v), d_v.ptr, len(idx), d_i.ptr, None))  # first call: symbol look-up
+    capi._check(L.vkm_dev_sync(0))
+    free0, total = C.c_uint64(0), C.c_uint64(0)
+    capi._check(L.vkm_dev_mem_info(0, C.byref(free0), C.byref(total)))
+    for _ in range(25):
+        capi._check(L.vkm_generate_tangents_dev_noalloc(len(v), d_v.ptr, len(idx), d_i.ptr, None))
+    capi._check(L.vkm_dev_sync(0))
+    free1 = C.c_uint64(0)
+    capi._check(L.vkm_dev_mem_info(0, C.byref(free1), C.byref(total)))
+    assert free1.value == free0.value, (free0.value, free1.value)
+    d_v.free()
+    d_i.free()
 
 
 def test_noalloc_rejects_sizes_beyond_the_built_in_scratch():

@@ -35,7 +35,7 @@ SYMBOLS = [
     "vkm_rangealloc_create", "vkm_rangealloc_destroy", "vkm_rangealloc_alloc", "vkm_rangealloc_free",
     "vkm_rangealloc_free_space", "vkm_pool_create", "vkm_pool_destroy", "vkm_pool_vertex_buffer",
     "vkm_pool_index_buffer", "vkm_pool_acquire", "vkm_pool_release",
-    "vkm_dev_alloc", "vkm_dev_free", "vkm_dev_upload", "vkm_dev_download", "vkm_dev_sync",
+    "vkm_dev_alloc", "vkm_dev_free", "vkm_dev_upload", "vkm_dev_download", "vkm_dev_sync", "vkm_dev_mem_info",
 ]
 
 
@@ -200,6 +200,7 @@ def lib():
     L.vkm_dev_upload.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint64]
     L.vkm_dev_download.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_uint64]
     L.vkm_dev_sync.argtypes = [C.c_int]
+    L.vkm_dev_mem_info.argtypes = [C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     _lib = L
     return L
 

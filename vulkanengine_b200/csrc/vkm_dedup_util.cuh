@@ -86,21 +86,46 @@ __global__ void __launch_bounds__(kThreads) k_dd_match(const float4* __restrict_
 }
 
 // One warp walks ucount_{i+1} = ucount_i + !(m_i < ucount_i); rank[i] = ucount_i, found[i] in bit 31.
+// The recurrence is sequential, but for a chunk of 32 vertices that starts at count u0 almost every lane is decided
+// without it: m < u0 is found whatever happens inside the chunk (the count only grows), m >= u0 + lane is not found
+// whatever happens (the count grows by at most one per vertex).  Only when some lane falls in between does the warp
+// replay that chunk one vertex at a time.  Four chunks of m are loaded ahead, so the walk is not paced by load latency.
 __global__ void k_dd_sequence(const uint32_t* __restrict__ m, uint32_t n, uint32_t* rank_found, uint32_t* out_count) {
     const uint32_t lane = threadIdx.x;
+    const uint32_t lt = (1u << lane) - 1u;
     uint32_t u = 0;
-    for (uint32_t base = 0; base < n; base += 32) {
-        const uint32_t i = base + lane;
-        const uint32_t mi = (i < n) ? m[i] : kNoMatch;
-        uint32_t mine = 0;
-        const uint32_t cnt = min(32u, n - base);
-        for (uint32_t k = 0; k < cnt; ++k) {
-            const uint32_t mk = __shfl_sync(0xFFFFFFFFu, mi, k);
-            const bool found = mk < u;
-            if (lane == k) mine = u | (found ? 0x80000000u : 0u);
-            u += found ? 0u : 1u;
+    for (uint32_t base0 = 0; base0 < n; base0 += 128) {
+        uint32_t mm[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t i = base0 + 32 * q + lane;
+            mm[q] = (i < n) ? m[i] : kNoMatch;
         }
-        if (i < n) rank_found[i] = mine;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t base = base0 + 32 * q;
+            if (base >= n) break;
+            const uint32_t i = base + lane, mi = mm[q];
+            const bool live = i < n;
+            const bool surely_found = live && mi < u;
+            const bool surely_new = live && (mi == kNoMatch || mi >= u + lane);
+            uint32_t mine;
+            if (__all_sync(0xFFFFFFFFu, !live || surely_found || surely_new)) {
+                const uint32_t news = __ballot_sync(0xFFFFFFFFu, surely_new);
+                mine = (u + __popc(news & lt)) | (surely_found ? 0x80000000u : 0u);
+                u += __popc(news);
+            } else {
+                mine = 0;
+                const uint32_t cnt = min(32u, n - base);
+                for (uint32_t k = 0; k < cnt; ++k) {
+                    const uint32_t mk = __shfl_sync(0xFFFFFFFFu, mi, k);
+                    const bool found = mk < u;
+                    if (lane == k) mine = u | (found ? 0x80000000u : 0u);
+                    u += found ? 0u : 1u;
+                }
+            }
+            if (live) rank_found[i] = mine;
+        }
     }
     if (lane == 0) *out_count = u;
 }

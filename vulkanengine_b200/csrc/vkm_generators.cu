@@ -13,6 +13,7 @@
 #include <cstring>
 
 extern "C" void vkm_internal_set_error(const char* msg);
+extern "C" int vkm_internal_device(int* sm);  // vkmesh.cu
 
 namespace {
 
@@ -74,6 +75,13 @@ int vkm_generate_plane_config(float width, float height, uint32_t xs, uint32_t y
         vkm_internal_set_error("no CUDA device (there is no CPU path)");
         return VKM_ERR_NO_DEVICE;
     }
+    int sms = 148;
+    const int dev = vkm_internal_device(&sms);  // the device selected with vkm_init()
+    if (dev >= ndev || cudaSetDevice(dev) != cudaSuccess) {
+        cudaGetLastError();
+        vkm_internal_set_error("vkm_generate_plane_config: the device chosen with vkm_init is not available");
+        return VKM_ERR_NO_DEVICE;
+    }
     float4* d_v = nullptr;
     uint32_t* d_i = nullptr;
     int rc = VKM_OK;
@@ -82,7 +90,7 @@ int vkm_generate_plane_config(float width, float height, uint32_t xs, uint32_t y
     if (!hv || !hi) rc = VKM_ERR_OOM;
     if (rc == VKM_OK && (cudaMalloc(&d_v, nseg * 4 * 64) != cudaSuccess || cudaMalloc(&d_i, nseg * 6 * 4) != cudaSuccess)) rc = VKM_ERR_OOM;
     if (rc == VKM_OK) {
-        k_plane<<<(unsigned)std::min<uint64_t>((nseg + 255) / 256, 148 * 8), 256>>>(d_v, d_i, xs, ys, width, height, tile_x, tile_y);
+        k_plane<<<(unsigned)std::min<uint64_t>((nseg + 255) / 256, (uint64_t)sms * 8), 256>>>(d_v, d_i, xs, ys, width, height, tile_x, tile_y);
         if (cudaMemcpy(hv, d_v, nseg * 4 * 64, cudaMemcpyDeviceToHost) != cudaSuccess ||
             cudaMemcpy(hi, d_i, nseg * 6 * 4, cudaMemcpyDeviceToHost) != cudaSuccess) {
             vkm_internal_set_error(cudaGetErrorString(cudaGetLastError()));

@@ -777,6 +777,17 @@ __global__ void __launch_bounds__(kThreads) k_face_frames(float4* vtx, const uin
     }
 }
 
+// Packs one column of the 64-byte vertex records (word offset `woff`, `nw` words: tangent = 12/4, normal = 3/3) into a
+// dense array: the host utilities bring back only what they changed.
+__global__ void __launch_bounds__(kThreads) k_pack_column(const float* __restrict__ vtx, uint32_t vertex_count, uint32_t woff,
+                                                          uint32_t nw, float* __restrict__ out) {
+    const uint64_t total = (uint64_t)vertex_count * nw;
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t v = i / nw;
+        out[i] = vtx[v * 16 + woff + (uint32_t)(i - v * nw)];
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Batches of small meshes (vkm_import_batch): several meshes, each with attribute arrays of its own, are laid
 // end to end in one set of device arrays and imported as ONE multi-shape stream.  This kernel turns every

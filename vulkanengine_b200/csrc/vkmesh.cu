@@ -946,7 +946,9 @@ struct HostCtx {
     DevBuf<float> pos, nrm, uv;
     DevBuf<int32_t> idx;
     DevBuf<float4> vtx;
-    DevBuf<uint32_t> ind, scratch, flag;
+    DevBuf<uint32_t> ind, scratch, flag, col;
+    DevBuf<uint32_t> dd_head, dd_next, dd_m, dd_rf, dd_cnt;  // vkm_deduplicate_vertices scratch, kept between calls
+    DevBuf<float4> dd_out;
     cudaStream_t st = nullptr;
     int bound_device = -1;
     // pinned bounce buffer + per-chunk events for the device-to-host leg of vkm_import_shapes
@@ -1185,7 +1187,8 @@ int ctx_bind(HostCtx& c) {
     if (c.bound_device != dev) {
         if (c.plan) { vkm_plan_destroy(c.plan); c.plan = nullptr; }
         c.pos.release(); c.nrm.release(); c.uv.release(); c.idx.release(); c.vtx.release(); c.ind.release();
-        c.scratch.release(); c.flag.release(); c.spans.release(); c.span_bad.release();
+        c.scratch.release(); c.flag.release(); c.spans.release(); c.span_bad.release(); c.col.release();
+        c.dd_head.release(); c.dd_next.release(); c.dd_m.release(); c.dd_rf.release(); c.dd_cnt.release(); c.dd_out.release();
         for (auto e : c.chunk_ev) cudaEventDestroy(e);  // events belong to the device they were created on
         c.chunk_ev.clear();
         release_upload_ring(c);
@@ -1208,16 +1211,46 @@ int frames_host(int mode, uint32_t vc, void* vertices, uint32_t ic, const uint32
     if ((rc = c.ind.ensure(ic))) return rc;
     if ((rc = c.scratch.ensure(vc))) return rc;
     if ((rc = c.flag.ensure(1))) return rc;
+    // Only the column the utility changes comes back: tangent (16 of the 64 bytes) or normal (12).  It is packed on
+    // the device, copied in one piece into page-locked staging together with the error flag (one synchronisation for
+    // the whole call), and scattered into the caller's interleaved array by a few host threads.
+    const uint32_t col_bytes = mode == 0 ? 16u : 12u, col_off = mode == 0 ? 48u : 12u;
+    const uint64_t packed_bytes = (uint64_t)vc * col_bytes;
+    if ((rc = c.col.ensure((packed_bytes + 3) / 4 + 4))) return rc;
+    if (packed_bytes + 64 > c.h_stage_cap) {
+        if (c.h_stage) cudaFreeHost(c.h_stage);
+        c.h_stage = nullptr;
+        c.h_stage_cap = 0;
+        const uint64_t want = packed_bytes + packed_bytes / 8 + 4096;
+        if (cudaMallocHost((void**)&c.h_stage, want) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(VKM_ERR_OOM, "pinned staging buffer (%llu bytes) could not be allocated", (unsigned long long)want);
+        }
+        c.h_stage_cap = want;
+    }
     CU(cudaMemcpyAsync(c.vtx.p, vertices, (uint64_t)vc * 64, cudaMemcpyHostToDevice, c.st));
     CU(cudaMemcpyAsync(c.ind.p, indices, (uint64_t)ic * 4, cudaMemcpyHostToDevice, c.st));
     CU(cudaMemsetAsync(c.flag.p, 0, 4, c.st));
     if ((rc = frames_dev(mode, vc, c.vtx.p, ic, c.ind.p, c.scratch.p, c.st, c.flag.p))) return rc;
-    uint32_t bad = 0;
-    CU(cudaMemcpyAsync(&bad, c.flag.p, 4, cudaMemcpyDeviceToHost, c.st));
+    k_pack_column<<<grid_for(vc, kThreads, c.bound_device), kThreads, 0, c.st>>>((const float*)c.vtx.p, vc, col_off / 4,
+                                                                                col_bytes / 4, (float*)c.col.p);
+    CU(cudaGetLastError());
+    uint32_t* h_flag = reinterpret_cast<uint32_t*>(c.h_stage + ((packed_bytes + 15) & ~15ull));
+    CU(cudaMemcpyAsync(c.h_stage, c.col.p, packed_bytes, cudaMemcpyDeviceToHost, c.st));
+    CU(cudaMemcpyAsync(h_flag, c.flag.p, 4, cudaMemcpyDeviceToHost, c.st));
     CU(cudaStreamSynchronize(c.st));
-    if (bad) return fail(VKM_ERR_BAD_INDEX, "an index is >= vertex_count (undefined behaviour in the reference)");
-    CU(cudaMemcpyAsync(vertices, c.vtx.p, (uint64_t)vc * 64, cudaMemcpyDeviceToHost, c.st));
-    CU(cudaStreamSynchronize(c.st));
+    if (*h_flag) return fail(VKM_ERR_BAD_INDEX, "an index is >= vertex_count (undefined behaviour in the reference)");
+    {
+        const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        const unsigned nthreads = (unsigned)std::min<uint64_t>(std::min(8u, hw), std::max<uint64_t>(1, vc / 65536));
+        char* dst = (char*)vertices;
+        const char* src = c.h_stage;
+        auto work = [&](unsigned t) {
+            const uint64_t a = (uint64_t)vc * t / nthreads, b = (uint64_t)vc * (t + 1) / nthreads;
+            for (uint64_t v = a; v < b; ++v) memcpy(dst + v * 64 + col_off, src + v * col_bytes, col_bytes);
+        };
+        HelperPool::get().run(nthreads, work);
+    }
     return VKM_OK;
 }
 
@@ -1259,7 +1292,8 @@ static void release_ctx(HostCtx& c) {
     cudaSetDevice(c.bound_device);
     if (c.plan) { vkm_plan_destroy(c.plan); c.plan = nullptr; }
     c.pos.release(); c.nrm.release(); c.uv.release(); c.idx.release(); c.vtx.release(); c.ind.release();
-    c.scratch.release(); c.flag.release(); c.spans.release(); c.span_bad.release();
+    c.scratch.release(); c.flag.release(); c.spans.release(); c.span_bad.release(); c.col.release();
+    c.dd_head.release(); c.dd_next.release(); c.dd_m.release(); c.dd_rf.release(); c.dd_cnt.release(); c.dd_out.release();
     if (c.h_stage) cudaFreeHost(c.h_stage);
     c.h_stage = nullptr;
     c.h_stage_cap = 0;
@@ -1288,9 +1322,10 @@ static int dedup_host(uint32_t vc, const void* vertices, uint32_t ic, uint32_t* 
     }
     uint32_t buckets = 1024;
     while (buckets < 2ull * vc && buckets < (1u << 30)) buckets <<= 1;
-    DevBuf<float4> out;
-    DevBuf<uint32_t> head, next, m, rf, cnt;
-    auto cleanup = [&]() { out.release(); head.release(); next.release(); m.release(); rf.release(); cnt.release(); };
+    // scratch lives in the host context and is reused (six cudaMalloc / cudaFree per call cost more than the kernels)
+    DevBuf<float4>& out = c.dd_out;
+    DevBuf<uint32_t>&head = c.dd_head, &next = c.dd_next, &m = c.dd_m, &rf = c.dd_rf, &cnt = c.dd_cnt;
+    auto cleanup = [&]() {};
     if ((rc = c.vtx.ensure((uint64_t)vc * 4)) || (rc = c.ind.ensure(std::max<uint32_t>(ic, 1))) ||
         (rc = out.ensure((uint64_t)vc * 4)) || (rc = head.ensure(buckets)) || (rc = next.ensure(vc)) ||
         (rc = m.ensure(vc)) || (rc = rf.ensure(vc)) || (rc = cnt.ensure(1))) {
@@ -1696,6 +1731,17 @@ int vkm_set_result_memory(int mode) {
     return VKM_OK;
 }
 
+// for the library's other translation units: the device chosen with vkm_init (first ordinal) and its SM count
+int vkm_internal_device(int* sm) {
+    int dev;
+    {
+        std::lock_guard<std::mutex> lk(g_ctx.mu);
+        dev = g_ctx.devices[0];
+    }
+    if (sm) *sm = sm_count(dev);
+    return dev;
+}
+
 // for the library's other translation units: fn(ctx, 0) .. fn(ctx, n-1) on the helper pool
 void vkm_internal_parallel_run(unsigned n, void (*fn)(void*, unsigned), void* ctx) {
     HelperPool::get().run(n, [&](unsigned i) { fn(ctx, i); });
@@ -1731,6 +1777,14 @@ int vkm_dev_upload(int device, void* d_dst, const void* h_src, uint64_t bytes) {
 int vkm_dev_download(int device, void* h_dst, const void* d_src, uint64_t bytes) {
     CU(cudaSetDevice(device));
     CU(cudaMemcpy(h_dst, d_src, bytes, cudaMemcpyDeviceToHost));
+    return VKM_OK;
+}
+int vkm_dev_mem_info(int device, uint64_t* free_bytes, uint64_t* total_bytes) {
+    CU(cudaSetDevice(device));
+    size_t f = 0, t = 0;
+    CU(cudaMemGetInfo(&f, &t));
+    if (free_bytes) *free_bytes = f;
+    if (total_bytes) *total_bytes = t;
     return VKM_OK;
 }
 int vkm_dev_sync(int device) {
