@@ -130,6 +130,20 @@ __device__ __forceinline__ uint32_t find_shape(const uint32_t* __restrict__ shap
     return lo;
 }
 
+// The same for a warp whose lanes mostly fall into one shape (neighbouring corners / slots): the first active lane
+// searches, the others check its answer with two loads and search themselves only when it does not fit.  With
+// thousands of shapes the plain search is 14 dependent loads per thread.
+__device__ __forceinline__ uint32_t find_shape_near(const uint32_t* __restrict__ shape_off, uint32_t nshapes, uint32_t c) {
+    if (nshapes <= 1) return 0;
+    const uint32_t mask = __activemask();
+    const int leader = __ffs(mask) - 1;
+    uint32_t hint = 0;
+    if ((int)(threadIdx.x & 31) == leader) hint = find_shape(shape_off, nshapes, c);
+    hint = __shfl_sync(mask, hint, leader);
+    if (__ldg(shape_off + hint) <= c && c < __ldg(shape_off + hint + 1)) return hint;
+    return find_shape(shape_off, nshapes, c);
+}
+
 // Monotone float -> uint map (so that integer atomicMin/Max order floats).  Never fed NaN.
 __device__ __forceinline__ uint32_t enc_float(float f) {
     const uint32_t b = __float_as_uint(f);

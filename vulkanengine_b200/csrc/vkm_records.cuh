@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(kThreads, VKM_REC_MINB) k_insert_records(Impor
         }
         uint32_t sh = 0, sh_begin = 0, sh_end = a.ncorners;
         if (MULTI) {
-            sh = find_shape(a.shape_off, a.nshapes, min(c0, a.ncorners - 1));
+            sh = find_shape_near(a.shape_off, a.nshapes, min(c0, a.ncorners - 1));
             sh_begin = a.shape_off[sh];
             sh_end = a.shape_off[sh + 1];
         }
@@ -272,7 +272,7 @@ __global__ void __launch_bounds__(kThreads) k_write_indices_rec(ImportArgs a) {
         for (int i = 0; i < 4; ++i) li[i] = __ldg(a.vid_of + min(s[i], nslots - 1));
         uint32_t sh = 0, sh_end = a.ncorners, base = 0;
         if (MULTI) {
-            sh = find_shape(a.shape_off, a.nshapes, min(c0, a.ncorners - 1));
+            sh = find_shape_near(a.shape_off, a.nshapes, min(c0, a.ncorners - 1));
             sh_end = a.shape_off[sh + 1];
             base = a.vbase[sh];
         }
@@ -395,7 +395,7 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
         uint32_t mn[3] = {neutral, neutral, neutral}, mx[3] = {neutral, neutral, neutral};
         uint32_t bsh = 0xFFFFFFFFu;
         if (first < a.ncorners) {
-            const uint32_t sh = MULTI ? find_shape(a.shape_off, a.nshapes, first) : 0u;
+            const uint32_t sh = MULTI ? find_shape_near(a.shape_off, a.nshapes, first) : 0u;
             const uint32_t id = lid;
             if (id < a.vertex_capacity) {
                 const uint32_t lf = a.lastface[id];  // >= 1: the slot's own corners reference the vertex
@@ -408,9 +408,17 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
                 Tri tr;
 #pragma unroll
                 for (int q = 0; q < 3; ++q) {
+                    const uint32_t sq = min(__ldg(sl + q), nslots - 1);
+                    if (sq == s) {
+                        // this corner IS the vertex being written (a vertex is always a corner of its own last
+                        // triangle): its position and texcoord are already in registers
+                        tr.px[q] = __uint_as_float(k[0]); tr.py[q] = __uint_as_float(k[1]); tr.pz[q] = __uint_as_float(k[2]);
+                        tr.u[q] = __uint_as_float(k[6]); tr.v[q] = __uint_as_float(k[7]);
+                        continue;
+                    }
                     uint32_t cv, ct;
                     // (reading (v, vt) straight from the index stream instead: one hop less, 0.40 -> 0.44 ms)
-                    corner_v_t<KEY>(a, min(__ldg(sl + q), nslots - 1), 3 * f + q, cv, ct);
+                    corner_v_t<KEY>(a, sq, 3 * f + q, cv, ct);
                     const float* pp = a.pos + 3ull * min(cv, a.np - 1);
                     const float2 uu = __ldg(reinterpret_cast<const float2*>(a.uv) + min(ct, a.nt - 1));
                     tr.px[q] = __ldg(pp); tr.py[q] = __ldg(pp + 1); tr.pz[q] = __ldg(pp + 2);
@@ -431,7 +439,18 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
                     for (int i = 0; i < 8; ++i) kc[i] = canon_bits(k[i]);
                     probe_fingerprint(a, kc, sh);
                 }
+#ifndef VKM_VTX_ST128  // two 256-bit streaming stores per record (four 128-bit ones: 0.399 -> 0.387 ms the other way round)
+                {
+                    const float4 tg = tangent_of(tr);
+                    float* dst = reinterpret_cast<float*>(a.out_vtx + 4ull * id);
+                    asm volatile("st.global.cs.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(dst), "r"(k[0]), "r"(k[1]), "r"(k[2]),
+                                 "r"(k[3]), "r"(k[4]), "r"(k[5]), "r"(k[6]), "r"(k[7]) : "memory");
+                    asm volatile("st.global.cs.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(dst + 8), "f"(0.f), "f"(0.f), "f"(0.f),
+                                 "f"(0.f), "f"(tg.x), "f"(tg.y), "f"(tg.z), "f"(tg.w) : "memory");
+                }
+#else
                 store_vertex(a.out_vtx + 4ull * id, k, tangent_of(tr));
+#endif
             }
         }
         // bounding box: one set of (improvement-checked) atomics per warp when its slots share a shape
