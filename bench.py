@@ -217,7 +217,10 @@ def run_reference(args, rank, world, emit):
     mesh, desc, scaling = build_workload(args, 0, 1)
     threads = reference_threads(mesh, args.ref_threads)
     if len(mesh.shape_offsets) == 2:
-        threads = min(threads, max(args.steps, 1))
+        # whole waves: K imports on T threads take ceil(K / T) rounds; use the fewest threads that keep that round count
+        # (20 steps on 16 cores: two rounds of 10 rather than 16 + 4)
+        rounds = -(-max(args.steps, 1) // threads)
+        threads = min(threads, -(-max(args.steps, 1) // rounds))
     if args.warmup:
         cpu_reference_run(mesh, args.warmup, min(threads, args.warmup) if len(mesh.shape_offsets) == 2 else threads)
     value, kind, dt = cpu_reference_run(mesh, args.steps, threads)

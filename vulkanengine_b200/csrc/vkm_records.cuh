@@ -310,14 +310,27 @@ __global__ void __launch_bounds__(kThreads) k_write_indices_rec(ImportArgs a) {
 // U * 4 / 2^32 per import) only cost that re-run, never a wrong result.  Against linear probing over single words
 // this needs one round trip for the whole bucket and, at load 1/2, almost never a second bucket, so the lanes of
 // a warp stay together.
+// Multi-shape imports (MULTI): a shape is its own dedup domain, so it also gets its own stretch of the table, sized
+// by its share of the corners.  The slots of one shape are neighbours in the slot domain, hence a warp's probes stay
+// inside a few hundred kilobytes instead of scattering over the whole table (10 000-mesh batch: an 850 MB table, every
+// probe a DRAM and TLB miss otherwise).  A shape that needs more than its stretch holds overflows, and the re-run uses a
+// larger table / the general schedule.
+template <bool MULTI>
 __device__ __forceinline__ void probe_fingerprint(const ImportArgs& a, const uint32_t kc[8], uint32_t sh) {
     const uint64_t h = hash_key8(kc, sh, a.seed);
     uint32_t fp = (uint32_t)(h >> 32);
     if (fp == kEmpty32) fp = 0xFFFFFFFEu;
-    const uint32_t nb = a.m2 >> 3;
+    uint32_t b_lo = 0, nb = a.m2 >> 3;
+    if (MULTI) {
+        const uint64_t all = nb;
+        b_lo = (uint32_t)(all * __ldg(a.shape_off + sh) / a.ncorners);
+        const uint32_t b_hi = (uint32_t)(all * __ldg(a.shape_off + sh + 1) / a.ncorners);
+        nb = max(b_hi, b_lo + 1) - b_lo;  // (b_lo < all because the shape has corners)
+    }
     uint32_t b = reduce32((uint32_t)h, nb);
-    for (int probe = 0; probe < 256; ++probe) {
-        uint32_t* base = a.table2 + 8ull * b;
+    const int limit = (int)min(nb, 256u);
+    for (int probe = 0; probe < limit; ++probe) {
+        uint32_t* base = a.table2 + 8ull * (b_lo + b);
         uint32_t w[8];
         asm volatile("ld.global.cg.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                      : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
@@ -437,7 +450,7 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
                     uint32_t kc[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) kc[i] = canon_bits(k[i]);
-                    probe_fingerprint(a, kc, sh);
+                    probe_fingerprint<MULTI>(a, kc, sh);
                 }
 #ifndef VKM_VTX_ST128  // two 256-bit streaming stores per record (four 128-bit ones: 0.399 -> 0.387 ms the other way round)
                 {
