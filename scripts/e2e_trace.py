@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""Host-side time line of vkm_import_shapes on the 16M mesh (VKM_TRACE=1)."""
+"""Host-side time line of vkm_import_shapes on the 16M mesh (VKM_TRACE=1).  `--pageable`: inputs in ordinary numpy
+memory (the drop-in default: what integration/engine_shims.cpp passes)."""
 import ctypes as C, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -9,7 +10,10 @@ m = synth.grid(2896)
 L = capi.lib()
 def pin(a):
     p = L.vkm_host_alloc(a.nbytes); C.memmove(p, a.ctypes.data, a.nbytes); return p
-hp, hn, hu, hi = (pin(a) for a in (m.pos, m.nrm, m.uv, m.idx))
+if "--pageable" in sys.argv:
+    hp, hn, hu, hi = (a.ctypes.data for a in (m.pos, m.nrm, m.uv, m.idx))
+else:
+    hp, hn, hu, hi = (pin(a) for a in (m.pos, m.nrm, m.uv, m.idx))
 so = np.ascontiguousarray(m.shape_offsets, np.uint64)
 out = (capi.ShapeOut * 1)()
 for it in range(3):
