@@ -62,6 +62,8 @@ struct ImportArgs {
     uint32_t msec;
     uint32_t* vid_of;    // [nkey + msec] local vertex index of every slot (written by the vertex pass)
     uint32_t seed;       // hash generation of this run (see hash_triplet)
+    uint32_t* hbox;      // [6] order-encoded min / max of ALL position records (only steers the fingerprint table's bucket choice)
+    uint32_t cell_vpc;   // record schedule: vertices per spatial cell, in quarters (0 = scrambled bucket choice)
     // outputs
     uint32_t* out_idx;  // [ncorners] per-shape local indices
     float4* out_vtx;    // [vertex capacity * 4]

@@ -60,6 +60,7 @@ __global__ void __launch_bounds__(kThreads) k_clear_records(ImportArgs a) {
     for (uint32_t i = tid; i <= a.nwords; i += nth) a.fbits[i] = 0;
     for (uint32_t i = tid; i < a.nshapes * 6u; i += nth) a.ext_enc[i] = 0x80000000u;
     if (tid < sizeof(Status) / 4) reinterpret_cast<uint32_t*>(a.status)[tid] = 0;
+    if (tid < 6) a.hbox[tid] = tid < 3 ? 0xFFFFFFFFu : 0u;  // min words / max words of the position box (k_flag_records)
 }
 
 // Side table: triplets whose key record is owned by another variant (or by another shape).  Same protocol as
@@ -213,12 +214,45 @@ __global__ void __launch_bounds__(kThreads) k_flag_records(ImportArgs a) {
         const uint32_t c = __ldcs(a.sec_first + s);
         if (c < a.ncorners) atomicOr(a.fbits + (c >> 5), 1u << (c & 31));  // kEmpty32 >= ncorners
     }
+    // Box of a SAMPLE (every 8th record) of the finite position words, referenced or not: it only steers which bucket of
+    // the fingerprint table a value key starts in (store_cell_map below; positions outside it are clamped to the border
+    // cells), so it can cost locality, never correctness.
+    if (a.cell_vpc) {
+        uint32_t mn[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, mx[3] = {0u, 0u, 0u};
+        const uint32_t* pw = reinterpret_cast<const uint32_t*>(a.pos);
+        // (blocks of 256 consecutive records, every 8th block: whole sectors are used)
+        for (uint32_t r = ((tid >> 8) << 11) + (tid & 255u); r < a.np; r += (nth >> 8) << 11) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const uint32_t b = __ldg(pw + 3ull * r + k);
+                if (!nonfinite_bits(b)) {
+                    const uint32_t e = enc_float(__uint_as_float(canon_bits(b)));
+                    mn[k] = min(mn[k], e);
+                    mx[k] = max(mx[k], e);
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            mn[k] = __reduce_min_sync(0xFFFFFFFFu, mn[k]);
+            mx[k] = __reduce_max_sync(0xFFFFFFFFu, mx[k]);
+        }
+        if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                if (mn[k] < a.hbox[k]) atomicMin(a.hbox + k, mn[k]);
+                if (mx[k] > a.hbox[3 + k]) atomicMax(a.hbox + 3 + k, mx[k]);
+            }
+        }
+    }
 }
 
 // vid_of[slot] = the slot's GLOBAL vertex id (its rank among all vertex-creating corners; kEmpty32 for unused slots).
 // The index pass subtracts the shape's base, which it tracks per thread anyway.
+__device__ void store_cell_map(const ImportArgs& a);
 __global__ void __launch_bounds__(kThreads) k_rank_records(ImportArgs a) {
     pdl_enter();
+    if (blockIdx.x == 0 && threadIdx.x == 0) store_cell_map(a);
     const uint32_t nq = (a.nkey + 3) >> 2, tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
     for (uint32_t q = tid; q < nq; q += nth) {
         const uint4 c4 = __ldg(reinterpret_cast<const uint4*>(a.rfirst) + q);
@@ -315,8 +349,68 @@ __global__ void __launch_bounds__(kThreads) k_write_indices_rec(ImportArgs a) {
 // inside a few hundred kilobytes instead of scattering over the whole table (10 000-mesh batch: an 850 MB table, every
 // probe a DRAM and TLB miss otherwise).  A shape that needs more than its stretch holds overflows, and the re-run uses a
 // larger table / the general schedule.
+// Which bucket a value key starts in.  A scrambled hash sends neighbouring vertices to opposite ends of the table:
+// every probe is a random DRAM access (measured: 0.17 of the vertex pass's 0.38 ms on the 16.8 M grid).  For a single
+// shape in hash generation 0 the bucket comes from the key's POSITION instead -- its cell on a 2-D lattice over the two
+// longest axes of the position box, row-major -- so that vertices that are neighbours in space, which for a
+// coherently stored mesh are neighbours in the slot domain, start in neighbouring buckets: the table is swept, not
+// hammered.  Equal keys have equal positions, hence equal cells: the proof is untouched.  Meshes whose vertices pile up
+// in few cells (thin volumes, far outliers in the box) overflow the probe limit; the re-run's generation is >= 1 and
+// scrambles.
+// The map is worked out once per import by one thread of k_rank_records (box and vertex count are final by then) and
+// parked behind the box words: hbox[8..13] = {on, axes, cells per row, min0, min1, 1 / cell size}.
+__device__ __forceinline__ float pick3(uint32_t ax, float x, float y, float z) { return ax == 0 ? x : (ax == 1 ? y : z); }
+
+__device__ void store_cell_map(const ImportArgs& a) {
+    uint32_t* o = a.hbox + 8;
+    o[0] = 0;
+    if (a.cell_vpc == 0 || a.seed != 0 || a.nshapes > 1) return;
+    float mnx, mny, mnz, ex, ey, ez;
+    {
+        const uint32_t l0 = a.hbox[0], l1 = a.hbox[1], l2 = a.hbox[2], h0 = a.hbox[3], h1 = a.hbox[4], h2 = a.hbox[5];
+        if (l0 > h0 || l1 > h1 || l2 > h2) return;  // no finite position at all
+        mnx = dec_float(l0); mny = dec_float(l1); mnz = dec_float(l2);
+        ex = __fsub_rn(dec_float(h0), mnx); ey = __fsub_rn(dec_float(h1), mny); ez = __fsub_rn(dec_float(h2), mnz);
+    }
+    // the two longest axes, longest first
+    uint32_t s0 = 0, s1 = 1;
+    if (ex >= ey && ex >= ez) { s0 = 0; s1 = ey >= ez ? 1u : 2u; }
+    else if (ey >= ex && ey >= ez) { s0 = 1; s1 = ex >= ez ? 0u : 2u; }
+    else { s0 = 2; s1 = ex >= ey ? 0u : 1u; }
+    const float e0 = pick3(s0, ex, ey, ez), e1 = pick3(s1, ex, ey, ez);
+    // as many cells as four times the buckets: four lattice rows share a run of buckets (cell_bucket), so the lattice
+    // covers the table once and a bucket collects about (vertices / buckets) = 4 keys of its 8 words
+    const float cells = fmaxf(4.0f * (float)(a.m2 >> 3), 1.0f);
+    const float area = __fmul_rn(e0, e1);
+    if (!(area > 0.0f) || !(area < 3.0e38f)) return;  // a line, a point, or an overflowing box
+    const float h = __fsqrt_rn(__fdiv_rn(area, cells));
+    if (!(h > 0.0f)) return;
+    const float inv_h = __fdiv_rn(1.0f, h);
+    if (!(inv_h < 3.0e38f)) return;
+    o[1] = s0 | (s1 << 2);
+    o[2] = (uint32_t)fminf(__fmul_rn(e0, inv_h), 4.0e6f) + 2u;
+    o[3] = __float_as_uint(pick3(s0, mnx, mny, mnz));
+    o[4] = __float_as_uint(pick3(s1, mnx, mny, mnz));
+    o[5] = __float_as_uint(inv_h);
+    o[0] = 1;
+}
+
+__device__ __forceinline__ uint32_t cell_bucket(const uint32_t* __restrict__ cm, const uint32_t kc[8], uint32_t nb) {
+    const uint32_t axes = __ldg(cm + 1), g0 = __ldg(cm + 2);
+    const float min0 = __uint_as_float(__ldg(cm + 3)), min1 = __uint_as_float(__ldg(cm + 4)), inv_h = __uint_as_float(__ldg(cm + 5));
+    const float p0 = pick3(axes & 3u, __uint_as_float(kc[0]), __uint_as_float(kc[1]), __uint_as_float(kc[2]));
+    const float p1 = pick3(axes >> 2, __uint_as_float(kc[0]), __uint_as_float(kc[1]), __uint_as_float(kc[2]));
+    const float c0 = fminf(fmaxf(__fmul_rn(__fsub_rn(p0, min0), inv_h), 0.0f), 4.0e6f);
+    const float c1 = fminf(fmaxf(__fmul_rn(__fsub_rn(p1, min1), inv_h), 0.0f), 4.0e6f);
+    // four lattice rows share one run of buckets: a bucket collects about four vertices, from rows that the slot domain
+    // visits close together in time, and the table is swept once (a scrambled start per row group was tried: runs
+    // overlap like a Poisson process, a quarter of the table ends up over-full and the probes crawl: 0.31 -> 0.42 ms)
+    const uint64_t id = (uint64_t)(uint32_t)c0 + (uint64_t)((uint32_t)c1 >> 2) * g0;
+    return (uint32_t)(id % nb);
+}
+
 template <bool MULTI>
-__device__ __forceinline__ void probe_fingerprint(const ImportArgs& a, const uint32_t kc[8], uint32_t sh) {
+__device__ __forceinline__ void probe_fingerprint(const ImportArgs& a, bool spatial, const uint32_t kc[8], uint32_t sh) {
     const uint64_t h = hash_key8(kc, sh, a.seed);
     uint32_t fp = (uint32_t)(h >> 32);
     if (fp == kEmpty32) fp = 0xFFFFFFFEu;
@@ -327,7 +421,7 @@ __device__ __forceinline__ void probe_fingerprint(const ImportArgs& a, const uin
         const uint32_t b_hi = (uint32_t)(all * __ldg(a.shape_off + sh + 1) / a.ncorners);
         nb = max(b_hi, b_lo + 1) - b_lo;  // (b_lo < all because the shape has corners)
     }
-    uint32_t b = reduce32((uint32_t)h, nb);
+    uint32_t b = (!MULTI && spatial) ? cell_bucket(a.hbox + 8, kc, nb) : reduce32((uint32_t)h, nb);
     const int limit = (int)min(nb, 256u);
     for (int probe = 0; probe < limit; ++probe) {
         uint32_t* base = a.table2 + 8ull * (b_lo + b);
@@ -388,6 +482,7 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
     const uint32_t padded = (nslots + 31) & ~31u;  // whole warps for the box reduction
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t neutral = 0x80000000u;
+    const bool spatial = !MULTI && __ldg(a.hbox + 8) != 0;
     for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < padded; s += gridDim.x * blockDim.x) {
         uint32_t first = kEmpty32, lid = kEmpty32, v = 0, n = 0, t = 0;
         if (s < a.nkey) {
@@ -421,7 +516,11 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
                 Tri tr;
 #pragma unroll
                 for (int q = 0; q < 3; ++q) {
+#ifdef VKM_DIAG_NOTAN
+                    const uint32_t sq = s;
+#else
                     const uint32_t sq = min(__ldg(sl + q), nslots - 1);
+#endif
                     if (sq == s) {
                         // this corner IS the vertex being written (a vertex is always a corner of its own last
                         // triangle): its position and texcoord are already in registers
@@ -450,7 +549,9 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
                     uint32_t kc[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) kc[i] = canon_bits(k[i]);
-                    probe_fingerprint<MULTI>(a, kc, sh);
+#ifndef VKM_DIAG_NOFP
+                    probe_fingerprint<MULTI>(a, spatial, kc, sh);
+#endif
                 }
 #ifndef VKM_VTX_ST128  // two 256-bit streaming stores per record (four 128-bit ones: 0.399 -> 0.387 ms the other way round)
                 {

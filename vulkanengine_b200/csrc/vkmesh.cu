@@ -309,7 +309,9 @@ struct vkm_plan {
     bool records_off = false;      // sticky: the side table would outgrow the slot arrays -> general schedule only
     uint32_t msec = 0;             // side-table slots of the record schedule
     uint32_t m2_pct = 200;         // record schedule: value-table slots per 100 key records
-    DevBuf<uint32_t> sec_first;
+    DevBuf<uint32_t> sec_first, hbox;
+    bool cell_on = true;           // record schedule: position-ordered bucket choice in the fingerprint table (VKM_CELL=0: off)
+    bool cell_off = false;         // sticky: a mesh piled its vertices up in few cells and overflowed the probe limit
     uint32_t seed = 0;             // hash generation (bumped when a table overflows: see hash_triplet)
     vkm_plan_stats stats{};        // of the import in flight / last finished
     DevBuf<uint32_t> table1, table2;
@@ -454,8 +456,12 @@ int plan_enqueue(vkm_plan* p) {
         a.nkey = na_key;
         a.sec_first = p->sec_first.p;
         a.msec = p->msec;
+        a.hbox = p->hbox.p;
         a.vid_of = p->aux1.p;
         a.m2 = (uint32_t)std::min<uint64_t>(p->m2, (uint64_t)na_key * p->m2_pct / 100 + 1024) & ~7u;  // whole 8-word buckets
+        // position-ordered buckets pay when the table is too large to live in L2 (random probes then go to DRAM); a
+        // small table is cheaper scrambled (no position box to compute)
+        a.cell_vpc = (p->cell_on && !p->cell_off && a.nshapes == 1 && p->seed == 0 && (uint64_t)a.m2 * 4 >= (32ull << 20)) ? 4u : 0u;
         const uint32_t nslots = a.nkey + a.msec;
         const bool multi = a.nshapes > 1;
         const int key2 = (int)a.t1_sel * 2 + (multi ? 1 : 0);
@@ -626,6 +632,8 @@ int vkm_plan_create(const vkm_plan_desc* desc, vkm_plan** out) {
     if (const char* e = getenv("VKM_RECORDS")) p->records_off = atoi(e) == 0;
     if (const char* e = getenv("VKM_M2_PCT")) p->m2_pct = (uint32_t)std::max(100, atoi(e));
     chk(p->sec_first.ensure(p->msec));
+    chk(p->hbox.ensure(16));
+    if (const char* e = getenv("VKM_CELL")) p->cell_on = atoi(e) != 0;
     if (rc != VKM_OK) {
         vkm_plan_destroy(p);
         return rc;
@@ -654,7 +662,7 @@ void vkm_plan_destroy(vkm_plan* p) {
     p->table1.release(); p->table2.release(); p->slot1.release(); p->aux1.release(); p->fbits.release();
     p->fprefix.release(); p->block_sums.release(); p->ext_enc.release(); p->vbase.release(); p->lastface.release();
     p->out_idx.release(); p->shape_off.release(); p->out_vtx.release(); p->trip.release(); p->status.release();
-    p->sec_first.release();
+    p->sec_first.release(); p->hbox.release();
     if (p->h_status) cudaFreeHost(p->h_status);
     if (p->h_vbase) cudaFreeHost(p->h_vbase);
     if (p->h_ext) cudaFreeHost(p->h_ext);
@@ -749,6 +757,7 @@ int vkm_plan_finish(vkm_plan* p, vkm_plan_result* r) {
                 }
             }
             if (s.overflow2) {
+                if (p->args.cell_vpc) p->cell_off = true;  // vertices piled up in few cells: scrambled buckets from now on
                 if (p->args.m2 < (p->m2 & ~7u)) p->m2_pct = 1u << 20;  // use the whole value table from now on
                 else again = false;                                    // fall through to the general growth below
             }
