@@ -516,11 +516,7 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
                 Tri tr;
 #pragma unroll
                 for (int q = 0; q < 3; ++q) {
-#ifdef VKM_DIAG_NOTAN
-                    const uint32_t sq = s;
-#else
                     const uint32_t sq = min(__ldg(sl + q), nslots - 1);
-#endif
                     if (sq == s) {
                         // this corner IS the vertex being written (a vertex is always a corner of its own last
                         // triangle): its position and texcoord are already in registers
@@ -549,9 +545,7 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
                     uint32_t kc[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) kc[i] = canon_bits(k[i]);
-#ifndef VKM_DIAG_NOFP
                     probe_fingerprint<MULTI>(a, spatial, kc, sh);
-#endif
                 }
 #ifndef VKM_VTX_ST128  // two 256-bit streaming stores per record (four 128-bit ones: 0.399 -> 0.387 ms the other way round)
                 {
