@@ -41,6 +41,9 @@ WORKLOADS = {
     "grid1m": (708, None, "synthetic 1.0M-triangle grid mesh, configs[1]"),
     "highdup16m_perm": (2896, 0x5EED0003, "16.8M-triangle grid, seeded random face order (locality defeated)"),
     "grid64m": (5793, None, "67.1M-triangle grid (configs[4] base, without injections)"),
+    # configs[1]'s other shape: lat/long sphere with a texture seam and collapsed poles (key attribute = uv, seam variants
+    # in the side table, degenerate pole triangles with NaN tangents)
+    "sphere1m": (708, None, "synthetic 1.0M-triangle UV sphere (708 rings x 708 segments, seam + poles), configs[1]"),
     # strong scaling: a FIXED batch of independent meshes, LPT-partitioned over the ranks (configs[3])
     "batch10k": (None, None, "batch of 10k synthetic meshes (1k-100k triangles each, log-uniform), configs[3]"),
     # config 5: degenerate triangles, duplicated records, +-0 / 1-ulp twins, NaN -- the general (full) schedule
@@ -139,6 +142,8 @@ def build_workload(args, rank: int = 0, world: int = 1):
         mesh = sharding.build_shard(ns, parts[rank])
         desc += f"; {args.batch_meshes} meshes, LPT partition, imbalance {sharding.imbalance(tris, parts):.4f}"
         return mesh, desc, "strong"
+    if args.workload == "sphere1m":
+        return synth.uv_sphere(n, n), desc, "weak"
     if args.workload == "adversarial64m":
         return synth.adversarial(n, frac=2e-4, nan_frac=2e-5), desc, "weak"
     # independent meshes per rank: same shape family, different placement

@@ -30,6 +30,10 @@ if n is None:
 
     ns, tris = sharding.batch_sizes(10000)
     m = sharding.build_shard(ns, sharding.lpt_partition(tris, 1)[0])
+elif args.workload == "sphere1m":
+    m = synth.uv_sphere(n, n)
+elif args.workload == "adversarial64m":
+    m = synth.adversarial(n, frac=2e-4, nan_frac=2e-5)
 else:
     m = synth.grid(n, permute_seed=perm)
 dev = 0

@@ -55,6 +55,19 @@ def test_config3_16m_equals_reference(perm):
     assert stats["schedule"] == 0 and stats["runs"] == 1, stats  # the clean speculation stood
 
 
+def test_config2_uv_sphere_1m_equals_reference():
+    """SURVEY 8(d) config 2's second shape at its full size: 708 x 708 lat/long sphere = 1 002 528 triangles, texture
+    seam (position records shared by two uv records: the side table of the record schedule), collapsed poles (zero-area
+    triangles, NaN tangents), key attribute = vt."""
+    m = synth.uv_sphere(708, 708)
+    assert m.triangles == 1_002_528 and len(m.uv) > len(m.pos)
+    capi.shutdown()
+    got, want, stats = _both(m)
+    assert_shapes_equal(got, want)
+    assert stats["schedule"] == 0, stats  # clean: distinct triplets carry distinct values
+    assert np.isnan(want[0].vertices["tangent"]).any()  # the pole triangles are degenerate
+
+
 def test_config5_adversarial_64m_equals_reference():
     m = synth.adversarial(5793, frac=2e-4, nan_frac=2e-5)
     # + keys that cluster in the build's own hashes (at this table size a 2048-probe overflow would need > 1e9
