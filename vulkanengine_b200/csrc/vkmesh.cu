@@ -447,7 +447,11 @@ int plan_enqueue(vkm_plan* p) {
     for (int i = 0; i < PH_COUNT; ++i) p->ev_phase[slot][i] = i;
     cudaError_t le = cudaSuccess;
     auto L = [&](cudaError_t e) { if (le == cudaSuccess) le = e; };
-    const bool P = !T && a.ncorners < (6u << 20);  // programmatic dependent launch: see below
+    // Programmatic dependent launch between the kernels of one import (not across the event records of timing mode, and
+    // not for the clear kernel, whose predecessor in the stream is a copy): 1 M triangles 0.112 -> 0.103 ms per import,
+    // 16.8 M neutral (0.822 -> 0.821).  VKM_PDL=0 switches it off.
+    static const bool pdl_on = !(getenv("VKM_PDL") && atoi(getenv("VKM_PDL")) == 0);
+    const bool P = !T && pdl_on;
     if (use_rec) {
         a.t1_mode = 0;
         a.t1_sel = (a.np >= a.nn && a.np >= a.nt) ? 0u : (a.nn >= a.nt ? 1u : 2u);
@@ -514,6 +518,7 @@ int plan_enqueue(vkm_plan* p) {
         }
         if (T) CU(cudaEventRecord(ev[e++], st));
     } else {
+    const bool Pg = P && a.ncorners < (6u << 20);  // general schedule: only for short kernels (measured in round 1, below)
     if (T) CU(cudaEventRecord(ev[PH_CLEAR], st));
     // Programmatic dependent launch between the kernels of one import (not across the event records of timing mode,
     // and not for k_clear, whose predecessor in the stream is a copy).  Only for imports whose kernels are short:
@@ -526,7 +531,7 @@ int plan_enqueue(vkm_plan* p) {
         const unsigned g1 = grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev);
         const int addr = a.t1_mode == 0 ? (int)a.t1_sel : 3;
         const bool multi = a.nshapes > 1;
-#define VKM_K1(A, M) L(launch_k(P, k_insert_triplets<A, M>, g1, kThreads, st, a))
+#define VKM_K1(A, M) L(launch_k(Pg, k_insert_triplets<A, M>, g1, kThreads, st, a))
         switch (addr * 2 + (multi ? 1 : 0)) {
             case 0: VKM_K1(0, false); break;
             case 1: VKM_K1(0, true); break;
@@ -541,27 +546,27 @@ int plan_enqueue(vkm_plan* p) {
     }
     if (T) CU(cudaEventRecord(ev[PH_VALUES], st));
     // short schedule: the value-level proof rides along in k_write_vertices<true>; only the flag bits are set here
-    if (full) L(launch_k(P, k_resolve_slots, grid_for(a.m1 / 2, kThreads, dev), kThreads, st, a, true));
-    else L(launch_k(P, k_flag_firsts, grid_for(a.m1 / 2, kThreads, dev), kThreads, st, a));
+    if (full) L(launch_k(Pg, k_resolve_slots, grid_for(a.m1 / 2, kThreads, dev), kThreads, st, a, true));
+    else L(launch_k(Pg, k_flag_firsts, grid_for(a.m1 / 2, kThreads, dev), kThreads, st, a));
     if (T) CU(cudaEventRecord(ev[PH_SCAN], st));
     if (full) {
-        L(launch_k(P, k_redo_flags_clear, grid_for(a.nwords, kThreads, dev), kThreads, st, a));
-        L(launch_k(P, k_redo_flags_mark, grid_for(a.m2, kThreads, dev), kThreads, st, a));
-        L(launch_k(P, k_mark_unmatchable, grid_for(a.ncorners, kThreads, dev), kThreads, st, a));
+        L(launch_k(Pg, k_redo_flags_clear, grid_for(a.nwords, kThreads, dev), kThreads, st, a));
+        L(launch_k(Pg, k_redo_flags_mark, grid_for(a.m2, kThreads, dev), kThreads, st, a));
+        L(launch_k(Pg, k_mark_unmatchable, grid_for(a.ncorners, kThreads, dev), kThreads, st, a));
     }
     const uint32_t ntiles = std::max<uint32_t>(1, (a.nwords + kScanTile - 1) / kScanTile);
-    L(launch_k(P, k_scan_tiles, ntiles, kScanThreads, st, a));
-    L(launch_k(P, k_scan_finish, ntiles, kScanThreads, st, a, ntiles, true));
+    L(launch_k(Pg, k_scan_tiles, ntiles, kScanThreads, st, a));
+    L(launch_k(Pg, k_scan_finish, ntiles, kScanThreads, st, a, ntiles, true));
     if (T) CU(cudaEventRecord(ev[PH_INDICES], st));
-    if (full) L(launch_k(P, k_final_index, grid_for(a.m1, kThreads, dev), kThreads, st, a));
-    L(launch_k(P, k_write_indices, grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, st, a));
+    if (full) L(launch_k(Pg, k_final_index, grid_for(a.m1, kThreads, dev), kThreads, st, a));
+    L(launch_k(Pg, k_write_indices, grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev), kThreads, st, a));
     if (T) CU(cudaEventRecord(ev[PH_VERTICES], st));
-    if (full) L(launch_k(P, k_write_vertices<false>, grid_for(a.m1 / 2, kThreads, dev, 6), kThreads, st, a));
-    else L(launch_k(P, k_write_vertices<true>, grid_for(a.m1 / 2, kThreads, dev, 6), kThreads, st, a));
-    if (full) L(launch_k(P, k_write_unmatchable_vertices, grid_for(a.ncorners, kThreads, dev), kThreads, st, a));
+    if (full) L(launch_k(Pg, k_write_vertices<false>, grid_for(a.m1 / 2, kThreads, dev, 6), kThreads, st, a));
+    else L(launch_k(Pg, k_write_vertices<true>, grid_for(a.m1 / 2, kThreads, dev, 6), kThreads, st, a));
+    if (full) L(launch_k(Pg, k_write_unmatchable_vertices, grid_for(a.ncorners, kThreads, dev), kThreads, st, a));
     if (T) CU(cudaEventRecord(ev[PH_TANGENTS], st));
     if (full)
-        L(launch_k(P, k_per_vertex_frames<0>, grid_for(a.vertex_capacity, kThreads, dev), kThreads, st, a.out_vtx,
+        L(launch_k(Pg, k_per_vertex_frames<0>, grid_for(a.vertex_capacity, kThreads, dev), kThreads, st, a.out_vtx,
                    (const uint32_t*)a.out_idx, (const uint32_t*)a.lastface, (const uint32_t*)&p->status.p->total_vertices,
                    a.vertex_capacity, (const uint32_t*)a.shape_off, (const uint32_t*)a.vbase, a.nshapes, a.vertex_capacity,
                    (const Status*)p->status.p));
