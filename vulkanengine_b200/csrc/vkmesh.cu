@@ -307,7 +307,9 @@ struct vkm_plan {
     bool ran_full = false;         // what the import in flight was launched with
     bool ran_records = false;      // the import in flight used the record schedule (vkm_records.cuh)
     bool records_off = false;      // sticky: the side table would outgrow the slot arrays -> general schedule only
+    bool records_off_env = false;  // VKM_RECORDS=0
     uint32_t msec = 0;             // side-table slots of the record schedule
+    uint32_t m2_pct_env = 200;     // the configured value (VKM_M2_PCT)
     uint32_t m2_pct = 200;         // record schedule: value-table slots per 100 key records
     DevBuf<uint32_t> sec_first, hbox;
     bool cell_on = true;           // record schedule: position-ordered bucket choice in the fingerprint table (VKM_CELL=0: off)
@@ -634,8 +636,8 @@ int vkm_plan_create(const vkm_plan_desc* desc, vkm_plan** out) {
     chk(p->status.ensure(1));
     // record schedule: side table for triplets that are not their key record's first variant (grown on overflow)
     p->msec = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(4096, p->desc.max_attrib / 8), 1u << 30);
-    if (const char* e = getenv("VKM_RECORDS")) p->records_off = atoi(e) == 0;
-    if (const char* e = getenv("VKM_M2_PCT")) p->m2_pct = (uint32_t)std::max(100, atoi(e));
+    if (const char* e = getenv("VKM_RECORDS")) p->records_off = p->records_off_env = atoi(e) == 0;
+    if (const char* e = getenv("VKM_M2_PCT")) p->m2_pct = p->m2_pct_env = (uint32_t)std::max(100, atoi(e));
     chk(p->sec_first.ensure(p->msec));
     chk(p->hbox.ensure(16));
     if (const char* e = getenv("VKM_CELL")) p->cell_on = atoi(e) != 0;
@@ -1430,7 +1432,13 @@ static int import_resident(HostCtx& c, const float* d_pos, uint64_t np, const fl
         if ((rc = vkm_plan_create(&d, &c.plan))) return rc;
         c.plan->grow_vertices = true;
     }
-    c.plan->t1_mode = 0;  // every host call is a new mesh: try the coherent addressing first
+    // every host call is a new mesh: whatever an earlier mesh forced on the plan (scrambled addressing, a later hash
+    // generation, no position-ordered buckets, no record schedule) is not held against this one
+    c.plan->t1_mode = 0;
+    c.plan->seed = 0;
+    c.plan->cell_off = false;
+    c.plan->records_off = c.plan->records_off_env;
+    c.plan->m2_pct = c.plan->m2_pct_env;
     if ((rc = vkm_plan_import(c.plan, d_pos, np, d_nrm, nn, d_uv, nt, d_idx, shape_off, nshapes, c.st))) return rc;
     vkm_plan_result r{};
     rc = vkm_plan_finish(c.plan, &r);
