@@ -623,7 +623,7 @@ def main():
             "dtype": "u32+f32", "data": "synthetic",
             "config": workload_config(args, mesh, desc, U, world), "unique_vertices_per_gpu": U,
             "roofline": roofline, "pipeline_roofline": pipeline_roofline, "schedules": schedules, "cpu_baseline": cpu_baseline, "e2e": e2e,
-            "gpu_launches": KERNELS_PER_STEP * args.steps, "clocks": clocks,
+            "gpu_launches": (13 if full else KERNELS_PER_STEP) * args.steps, "clocks": clocks,  # general schedule: 13 launches per import
         }
         emit(line)
     if world > 1:
