@@ -87,3 +87,33 @@ def test_adversarial_with_all_collision_kinds_matches_reference():
     m = hash_collide.inject(m, value_keys=600, triplet_keys=600, twin_pairs=2)
     got, st = _fresh_import(m, records=True)
     assert_shapes_equal(got, _ref(m))
+
+
+def test_plan_statistics_and_pointer_alignment_checks():
+    """vkm_plan_get_stats tells which schedule stood; vkm_plan_import refuses device pointers its vector loads cannot
+    take (a sub-range of a packed arena) instead of faulting."""
+    m = synth.grid(64)
+    d = [capi.DeviceArray(0, a) for a in (m.pos, m.nrm, m.uv, m.idx)]
+    na = max(len(m.pos), len(m.nrm), len(m.uv))
+    plan = capi.Plan(0, m.corners, max_attrib=na + 8, max_vertices=na + 1024)
+    plan.import_async(d[0].ptr, len(m.pos), d[1].ptr, len(m.nrm), d[2].ptr, len(m.uv), d[3].ptr, m.shape_offsets)
+    plan.finish()
+    st = plan.stats()
+    assert st == {"runs": 1, "schedule": 0, "mis_speculated": 0, "table_overflows": 0, "reseeds": 0, "hash_seed": 0}, st
+    dirty = synth.with_duplicate_record(m)
+    dp, di = capi.DeviceArray(0, dirty.pos), capi.DeviceArray(0, dirty.idx)
+    plan.import_async(dp.ptr, len(dirty.pos), d[1].ptr, len(m.nrm), d[2].ptr, len(m.uv), di.ptr, dirty.shape_offsets)
+    r = plan.finish()
+    st = plan.stats()
+    assert st["runs"] == 2 and st["schedule"] == 2 and st["mis_speculated"] == 1, st
+    assert int(r.total_vertices) == len(m.pos)  # the duplicated record merged
+    # misaligned index stream (4 bytes into the buffer) and texcoords (4 bytes in): rejected, nothing launched
+    with pytest.raises(capi.VkmError) as e:
+        plan.import_async(d[0].ptr, len(m.pos), d[1].ptr, len(m.nrm), d[2].ptr, len(m.uv), d[3].ptr + 4, m.shape_offsets)
+    assert e.value.code == 1 and "aligned" in str(e.value)
+    with pytest.raises(capi.VkmError) as e:
+        plan.import_async(d[0].ptr, len(m.pos), d[1].ptr, len(m.nrm), d[2].ptr + 4, len(m.uv) - 1, d[3].ptr, m.shape_offsets)
+    assert e.value.code == 1
+    plan.destroy()
+    for x in d + [dp, di]:
+        x.free()
