@@ -444,7 +444,7 @@ int plan_enqueue(vkm_plan* p) {
     // Record schedule (vkm_records.cuh): the clean-mesh speculation with 16-byte key records instead of the hashed table.
     const uint32_t na_key = std::max(a.np, std::max(a.nn, a.nt));
     const bool use_rec = !full && !p->records_off && p->t1_mode == 0 && a.ncorners > 0 && (uint64_t)na_key + 8 <= p->table1.n && (uint64_t)na_key / 2 + 2 <= p->trip.n &&
-                         (uint64_t)na_key + p->msec <= p->aux1.n && p->msec > 0;
+                         (uint64_t)na_key + 64 <= p->aux1.n && p->msec > 0;
     p->ran_records = use_rec;
     for (int i = 0; i < PH_COUNT; ++i) p->ev_phase[slot][i] = i;
     cudaError_t le = cudaSuccess;
@@ -461,7 +461,7 @@ int plan_enqueue(vkm_plan* p) {
         a.ident = reinterpret_cast<uint2*>(p->trip.p);
         a.nkey = na_key;
         a.sec_first = p->sec_first.p;
-        a.msec = p->msec;
+        a.msec = (uint32_t)std::min<uint64_t>(p->msec, p->aux1.n - na_key);  // vid_of (= aux1) holds nkey + msec slots
         a.hbox = p->hbox.p;
         a.vid_of = p->aux1.p;
         a.m2 = (uint32_t)std::min<uint64_t>(p->m2, (uint64_t)na_key * p->m2_pct / 100 + 1024) & ~7u;  // whole 8-word buckets
@@ -754,8 +754,8 @@ int vkm_plan_finish(vkm_plan* p, vkm_plan_result* r) {
             bool again = attempt <= 16;
             if (s.overflow1) {
                 const uint64_t cap = p->aux1.n > p->args.nkey ? p->aux1.n - p->args.nkey : 0;  // vid_of holds nkey + msec
-                if (p->msec < cap) {
-                    const uint64_t want = std::min<uint64_t>(cap, 4ull * p->msec);
+                if (p->args.msec < cap) {
+                    const uint64_t want = std::min<uint64_t>(cap, 4ull * std::max(p->msec, p->args.msec));
                     int rc;
                     if ((rc = p->sec_first.ensure(want))) return rc;
                     p->msec = (uint32_t)want;
