@@ -760,7 +760,10 @@ int vkm_plan_finish(vkm_plan* p, vkm_plan_result* r) {
                     if ((rc = p->sec_first.ensure(want))) return rc;
                     p->msec = (uint32_t)want;
                 } else {
-                    p->records_off = true;  // more seam variants than key records: the general schedule handles it
+                    // more seam variants than key records: the general schedule handles it -- with scrambled addressing
+                    // straight away (so many triplets per key record are what overflows its coherent addressing too)
+                    p->records_off = true;
+                    p->t1_mode = 1;
                 }
             }
             if (s.overflow2) {
