@@ -409,19 +409,25 @@ __device__ __forceinline__ uint32_t cell_bucket(const uint32_t* __restrict__ cm,
     return (uint32_t)(id % nb);
 }
 
+// Where the probe of a value key starts: fingerprint, first bucket, and (MULTI) the shape's stretch of the table.
 template <bool MULTI>
-__device__ __forceinline__ void probe_fingerprint(const ImportArgs& a, bool spatial, const uint32_t kc[8], uint32_t sh) {
+__device__ __forceinline__ void fingerprint_start(const ImportArgs& a, bool spatial, const uint32_t kc[8], uint32_t sh,
+                                                  uint32_t& fp, uint32_t& b, uint32_t& b_lo, uint32_t& nb) {
     const uint64_t h = hash_key8(kc, sh, a.seed);
-    uint32_t fp = (uint32_t)(h >> 32);
+    fp = (uint32_t)(h >> 32);
     if (fp == kEmpty32) fp = 0xFFFFFFFEu;
-    uint32_t b_lo = 0, nb = a.m2 >> 3;
+    b_lo = 0;
+    nb = a.m2 >> 3;
     if (MULTI) {
         const uint64_t all = nb;
         b_lo = (uint32_t)(all * __ldg(a.shape_off + sh) / a.ncorners);
         const uint32_t b_hi = (uint32_t)(all * __ldg(a.shape_off + sh + 1) / a.ncorners);
         nb = max(b_hi, b_lo + 1) - b_lo;  // (b_lo < all because the shape has corners)
     }
-    uint32_t b = (!MULTI && spatial) ? cell_bucket(a.hbox + 8, kc, nb) : reduce32((uint32_t)h, nb);
+    b = (!MULTI && spatial) ? cell_bucket(a.hbox + 8, kc, nb) : reduce32((uint32_t)h, nb);
+}
+
+__device__ __forceinline__ void probe_fingerprint(const ImportArgs& a, uint32_t fp, uint32_t b, uint32_t b_lo, uint32_t nb) {
     const int limit = (int)min(nb, 256u);
     for (int probe = 0; probe < limit; ++probe) {
         uint32_t* base = a.table2 + 8ull * (b_lo + b);
@@ -472,7 +478,7 @@ __device__ __forceinline__ void corner_v_t(const ImportArgs& a, uint32_t s, uint
 }
 
 #ifndef VKM_VTX_MINB
-#define VKM_VTX_MINB 6
+#define VKM_VTX_MINB 5
 #endif
 // Slot domain.  Also the pass that PROVES the import clean (NaN/Inf screen + fingerprint of every value key).
 template <int KEY, bool MULTI>
@@ -509,6 +515,17 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
                 const uint32_t lf = a.lastface[id];  // >= 1: the slot's own corners reference the vertex
                 uint32_t k[8];
                 gather_key(a, v, n, t, k);
+                // single shape: the fingerprint bucket is known as soon as the attributes are; ask L2 for it now, so that the
+                // tangent chain's round trips below cover its way in from DRAM (vertex pass 0.305 -> 0.286 ms on the
+                // 16.8 M grid, 1.21 -> 1.12 on the 67 M grid, together with 51 registers instead of 40)
+                uint32_t pf_fp = 0, pf_b = 0;
+                if (!MULTI) {
+                    uint32_t kc0[8], b_lo0, nb0;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) kc0[i] = canon_bits(k[i]);
+                    fingerprint_start<false>(a, spatial, kc0, 0u, pf_fp, pf_b, b_lo0, nb0);
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(a.table2 + 8ull * pf_b));
+                }
                 // the winning (highest-numbered) triangle: its gathers are issued before the fingerprint probe so that
                 // both chains are in flight together
                 const uint32_t f = min(max(lf, 1u) - 1u, (a.ncorners - 1) / 3);
@@ -541,11 +558,16 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
                 bsh = sh;
                 if (bad) {
                     a.status->has_unmatchable = 1;
-                } else {
-                    uint32_t kc[8];
+                } else if (MULTI) {
+                    // (starting the probe early as above was measured on the 10 000-mesh batch: 5.56 -> 5.61 ms, no gain --
+                    // a shape's stretch of the table is small enough to sit in L2 while the shape's slots go by)
+                    uint32_t kc[8], fp, b, b_lo, nb;
 #pragma unroll
                     for (int i = 0; i < 8; ++i) kc[i] = canon_bits(k[i]);
-                    probe_fingerprint<MULTI>(a, spatial, kc, sh);
+                    fingerprint_start<MULTI>(a, spatial, kc, sh, fp, b, b_lo, nb);
+                    probe_fingerprint(a, fp, b, b_lo, nb);
+                } else {
+                    probe_fingerprint(a, pf_fp, pf_b, 0u, a.m2 >> 3);
                 }
 #ifndef VKM_VTX_ST128  // two 256-bit streaming stores per record (four 128-bit ones: 0.399 -> 0.387 ms the other way round)
                 {
