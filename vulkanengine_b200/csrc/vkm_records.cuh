@@ -338,8 +338,9 @@ __global__ void __launch_bounds__(kThreads) k_write_indices_rec(ImportArgs a) {
 // The clean-import proof of the record schedule: every distinct triplet's canonical 8-float key leaves a 32-bit
 // fingerprint in a bucketed table (bucket = one 32-byte sector = 8 words, read with one 256-bit load).  Two EQUAL keys
 // hash to the same bucket sequence and the same fingerprint, and the later of them is guaranteed to see the earlier one
-// (a claim at word j has looked at every word before j, either in its snapshot or as the value its failed CAS
-// returned, and words never change once set): it raises has_value_dup, and vkm_plan_finish re-runs the import with
+// (every key walks the words of a bucket in an order of its own that equal keys share; a claim at a word has looked at
+// every word before it in that order, either in its snapshot or as the value its failed CAS returned, and words never
+// change once set): it raises has_value_dup, and vkm_plan_finish re-runs the import with
 // the general schedule, which decides exactly.  Two DIFFERENT keys with one fingerprint in one bucket (about
 // U * 4 / 2^32 per import) only cost that re-run, never a wrong result.  Against linear probing over single words
 // this needs one round trip for the whole bucket and, at load 1/2, almost never a second bucket, so the lanes of
@@ -378,8 +379,8 @@ __device__ void store_cell_map(const ImportArgs& a) {
     else if (ey >= ex && ey >= ez) { s0 = 1; s1 = ex >= ez ? 0u : 2u; }
     else { s0 = 2; s1 = ex >= ey ? 0u : 1u; }
     const float e0 = pick3(s0, ex, ey, ez), e1 = pick3(s1, ex, ey, ez);
-    // as many cells as four times the buckets: four lattice rows share a run of buckets (cell_bucket), so the lattice
-    // covers the table once and a bucket collects about (vertices / buckets) = 4 keys of its 8 words
+    // as many cells as four times the buckets: four consecutive cells of a row share a bucket (cell_bucket), so the
+    // lattice covers the table once and a bucket collects about (vertices / buckets) = 4 keys of its 8 words
     const float cells = fmaxf(4.0f * (float)(a.m2 >> 3), 1.0f);
     const float area = __fmul_rn(e0, e1);
     if (!(area > 0.0f) || !(area < 3.0e38f)) return;  // a line, a point, or an overflowing box
@@ -402,11 +403,14 @@ __device__ __forceinline__ uint32_t cell_bucket(const uint32_t* __restrict__ cm,
     const float p1 = pick3(axes >> 2, __uint_as_float(kc[0]), __uint_as_float(kc[1]), __uint_as_float(kc[2]));
     const float c0 = fminf(fmaxf(__fmul_rn(__fsub_rn(p0, min0), inv_h), 0.0f), 4.0e6f);
     const float c1 = fminf(fmaxf(__fmul_rn(__fsub_rn(p1, min1), inv_h), 0.0f), 4.0e6f);
-    // four lattice rows share one run of buckets: a bucket collects about four vertices, from rows that the slot domain
-    // visits close together in time, and the table is swept once (a scrambled start per row group was tried: runs
-    // overlap like a Poisson process, a quarter of the table ends up over-full and the probes crawl: 0.31 -> 0.42 ms)
-    const uint64_t id = (uint64_t)(uint32_t)c0 + (uint64_t)((uint32_t)c1 >> 2) * g0;
-    return (uint32_t)(id % nb);
+    // Four CONSECUTIVE cells of a lattice row share a bucket, each with its own pair of words (returned in bits 30-31):
+    // the lanes of a warp -- consecutive slots, for a coherently stored mesh consecutive cells of a row -- then touch 8
+    // sectors of the table instead of 32 and do not meet at the same word, and the table is swept once.  (Four lattice
+    // ROWS per bucket, one cell of each: every lane its own sector, vertex pass 0.286 -> 0.264 ms this way round.  A
+    // scrambled start per row group: runs overlap like a Poisson process, a quarter of the table ends up over-full and
+    // the probes crawl, 0.31 -> 0.42 ms.)
+    const uint64_t id = (uint64_t)((uint32_t)c0 >> 2) + (uint64_t)(uint32_t)c1 * ((g0 + 3u) >> 2);
+    return (uint32_t)(id % nb) | (((uint32_t)c0 & 3u) << 30);
 }
 
 // Where the probe of a value key starts: fingerprint, first bucket, and (MULTI) the shape's stretch of the table.
@@ -429,6 +433,8 @@ __device__ __forceinline__ void fingerprint_start(const ImportArgs& a, bool spat
 
 __device__ __forceinline__ void probe_fingerprint(const ImportArgs& a, uint32_t fp, uint32_t b, uint32_t b_lo, uint32_t nb) {
     const int limit = (int)min(nb, 256u);
+    const uint32_t rot = (b >> 30) * 2u;  // the key's own first word of every bucket (0 for hashed buckets)
+    b &= 0x3FFFFFFFu;
     for (int probe = 0; probe < limit; ++probe) {
         uint32_t* base = a.table2 + 8ull * (b_lo + b);
         uint32_t w[8];
@@ -445,8 +451,11 @@ __device__ __forceinline__ void probe_fingerprint(const ImportArgs& a, uint32_t 
         // ONE claim per lane at the lane's own first empty word (a per-word loop would make the warp walk all eight
         // words one atomic round trip at a time); a second turn only when another thread took that word meanwhile
         bool done = false;
+        // word order of this key: its own pair first, then round the bucket (equal keys have equal orders: the proof's
+        // argument runs along that order)
+        empties = ((empties >> rot) | (empties << (8u - rot))) & 0xFFu;
         while (!seen && !done && empties) {
-            const int j = __ffs(empties) - 1;
+            const int j = ((__ffs(empties) - 1) + (int)rot) & 7;
             const uint32_t prev = atomicCAS(base + j, kEmpty32, fp);
             if (prev == kEmpty32) done = true;
             else if (prev == fp) seen = true;
@@ -524,7 +533,7 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
 #pragma unroll
                     for (int i = 0; i < 8; ++i) kc0[i] = canon_bits(k[i]);
                     fingerprint_start<false>(a, spatial, kc0, 0u, pf_fp, pf_b, b_lo0, nb0);
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(a.table2 + 8ull * pf_b));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(a.table2 + 8ull * (pf_b & 0x3FFFFFFFu)));
                 }
                 // the winning (highest-numbered) triangle: its gathers are issued before the fingerprint probe so that
                 // both chains are in flight together
