@@ -501,8 +501,10 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
     for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < padded; s += gridDim.x * blockDim.x) {
         uint32_t first = kEmpty32, lid = kEmpty32, v = 0, n = 0, t = 0;
         if (s < a.nkey) {
-            first = __ldg(a.rfirst + s);
+            // (a used slot has a vertex id; the first corner itself is only needed to find the shape: 34 MB less to read
+            // on the 16.8 M grid, vertex pass 0.264 -> 0.259 ms)
             lid = __ldg(a.vid_of + s);
+            first = MULTI ? __ldg(a.rfirst + s) : (lid != kEmpty32 ? 0u : kEmpty32);
             const uint2 ab = __ldg(a.ident + s);
             join_triplet<KEY>(s, ab.x, ab.y, v, n, t);
         } else if (s < nslots) {
