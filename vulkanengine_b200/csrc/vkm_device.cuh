@@ -225,4 +225,86 @@ __device__ __forceinline__ void gather_key(const ImportArgs& a, uint32_t v, uint
     k[7] = tt.y;
 }
 
+// Box of a SAMPLE (every 8th block of 256 records) of the finite position words, referenced or not: it only steers where
+// in a value table a key starts (store_cell_map below; positions outside it are clamped to the border cells), so it can
+// cost locality, never correctness.  hbox[0..2] = min words, hbox[3..5] = max words (initialised by the clear kernels).
+__device__ __forceinline__ void sample_position_box(const ImportArgs& a, uint32_t tid, uint32_t nth) {
+    uint32_t mn[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, mx[3] = {0u, 0u, 0u};
+    const uint32_t* pw = reinterpret_cast<const uint32_t*>(a.pos);
+    // (blocks of 256 consecutive records, every 8th block: whole sectors are used)
+    for (uint32_t r = ((tid >> 8) << 11) + (tid & 255u); r < a.np; r += (nth >> 8) << 11) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const uint32_t b = __ldg(pw + 3ull * r + k);
+            if (!nonfinite_bits(b)) {
+                const uint32_t e = enc_float(__uint_as_float(canon_bits(b)));
+                mn[k] = min(mn[k], e);
+                mx[k] = max(mx[k], e);
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        mn[k] = __reduce_min_sync(0xFFFFFFFFu, mn[k]);
+        mx[k] = __reduce_max_sync(0xFFFFFFFFu, mx[k]);
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            if (mn[k] < a.hbox[k]) atomicMin(a.hbox + k, mn[k]);
+            if (mx[k] > a.hbox[3 + k]) atomicMax(a.hbox + 3 + k, mx[k]);
+        }
+    }
+}
+
+__device__ __forceinline__ float pick3(uint32_t ax, float x, float y, float z) { return ax == 0 ? x : (ax == 1 ? y : z); }
+
+__device__ __forceinline__ void store_cell_map(const ImportArgs& a) {
+    uint32_t* o = a.hbox + 8;
+    o[0] = 0;
+    if (a.cell_vpc == 0 || a.seed != 0 || a.nshapes > 1) return;
+    float mnx, mny, mnz, ex, ey, ez;
+    {
+        const uint32_t l0 = a.hbox[0], l1 = a.hbox[1], l2 = a.hbox[2], h0 = a.hbox[3], h1 = a.hbox[4], h2 = a.hbox[5];
+        if (l0 > h0 || l1 > h1 || l2 > h2) return;  // no finite position at all
+        mnx = dec_float(l0); mny = dec_float(l1); mnz = dec_float(l2);
+        ex = __fsub_rn(dec_float(h0), mnx); ey = __fsub_rn(dec_float(h1), mny); ez = __fsub_rn(dec_float(h2), mnz);
+    }
+    // the two longest axes, longest first
+    uint32_t s0 = 0, s1 = 1;
+    if (ex >= ey && ex >= ez) { s0 = 0; s1 = ey >= ez ? 1u : 2u; }
+    else if (ey >= ex && ey >= ez) { s0 = 1; s1 = ex >= ez ? 0u : 2u; }
+    else { s0 = 2; s1 = ex >= ey ? 0u : 1u; }
+    const float e0 = pick3(s0, ex, ey, ez), e1 = pick3(s1, ex, ey, ez);
+    // as many cells as four times the buckets: four consecutive cells of a row share a bucket (cell_bucket), so the
+    // lattice covers the table once and a bucket collects about (vertices / buckets) = 4 keys of its 8 words
+    const float cells = fmaxf(a.cell_vpc == 4 ? 4.0f * (float)(a.m2 >> 3) : (float)(a.m2 >> 1), 1.0f);  // (general schedule: a cell per pair of words)
+    const float area = __fmul_rn(e0, e1);
+    if (!(area > 0.0f) || !(area < 3.0e38f)) return;  // a line, a point, or an overflowing box
+    const float h = __fsqrt_rn(__fdiv_rn(area, cells));
+    if (!(h > 0.0f)) return;
+    const float inv_h = __fdiv_rn(1.0f, h);
+    if (!(inv_h < 3.0e38f)) return;
+    o[1] = s0 | (s1 << 2);
+    o[2] = (uint32_t)fminf(__fmul_rn(e0, inv_h), 4.0e6f) + 2u;
+    o[3] = __float_as_uint(pick3(s0, mnx, mny, mnz));
+    o[4] = __float_as_uint(pick3(s1, mnx, mny, mnz));
+    o[5] = __float_as_uint(inv_h);
+    o[0] = 1;
+}
+
+// General schedule: where a value key starts in its single-word table -- the lattice cell of its position, two words per
+// cell, row-major, so that neighbours in space (for a coherently stored mesh: in the slot domain) probe neighbouring
+// sectors instead of random ones.  Equal keys have equal positions, hence equal homes.
+__device__ __forceinline__ uint32_t cell_home(const uint32_t* __restrict__ cm, const uint32_t kc[8], uint32_t m2) {
+    const uint32_t axes = __ldg(cm + 1), g0 = __ldg(cm + 2);
+    const float min0 = __uint_as_float(__ldg(cm + 3)), min1 = __uint_as_float(__ldg(cm + 4)), inv_h = __uint_as_float(__ldg(cm + 5));
+    const float p0 = pick3(axes & 3u, __uint_as_float(kc[0]), __uint_as_float(kc[1]), __uint_as_float(kc[2]));
+    const float p1 = pick3(axes >> 2, __uint_as_float(kc[0]), __uint_as_float(kc[1]), __uint_as_float(kc[2]));
+    const float c0 = fminf(fmaxf(__fmul_rn(__fsub_rn(p0, min0), inv_h), 0.0f), 4.0e6f);
+    const float c1 = fminf(fmaxf(__fmul_rn(__fsub_rn(p1, min1), inv_h), 0.0f), 4.0e6f);
+    const uint64_t id = (uint64_t)(uint32_t)c0 + (uint64_t)(uint32_t)c1 * g0;
+    return (uint32_t)((2ull * id) % m2);
+}
+
 }  // namespace vkm

@@ -40,6 +40,22 @@ __global__ void __launch_bounds__(kThreads) k_clear(ImportArgs a) {
     for (uint32_t i = tid; i <= a.nwords; i += nth) a.fbits[i] = 0;
     for (uint32_t i = tid; i < a.nshapes * 6u; i += nth) a.ext_enc[i] = 0x80000000u;
     if (tid < sizeof(Status) / 4) reinterpret_cast<uint32_t*>(a.status)[tid] = 0;
+    if (a.cell_vpc) {  // position-ordered value table: sampled position box (k_sample_box), cell map off until k_cell_map
+        if (tid < 6) a.hbox[tid] = tid < 3 ? 0xFFFFFFFFu : 0u;
+        if (tid == 6) a.hbox[8] = 0;
+    }
+}
+
+// Position-ordered homes in the value table (insert_value): sample the position box, then one thread derives the
+// lattice (vkm_device.cuh).  Two short launches in front of the insert pass; only for single shapes with a table too
+// large for L2, in hash generation 0.
+__global__ void __launch_bounds__(kThreads) k_sample_box(ImportArgs a) {
+    pdl_enter();
+    sample_position_box(a, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
+}
+__global__ void k_cell_map(ImportArgs a) {
+    pdl_enter();
+    if (blockIdx.x == 0 && threadIdx.x == 0) store_cell_map(a);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -155,12 +171,12 @@ __device__ __forceinline__ bool same_value_key(const ImportArgs& a, uint32_t occ
 }
 
 __device__ __forceinline__ uint32_t insert_value(const ImportArgs& a, uint32_t c, const uint32_t k[8], uint32_t sh,
-                                                 uint32_t sh_begin, uint32_t sh_end) {
+                                                 uint32_t sh_begin, uint32_t sh_end, bool spatial) {
     const uint64_t h = hash_key8(k, sh, a.seed);
     const uint32_t cmask = (a.cbits >= 32) ? 0xFFFFFFFFu : ((1u << a.cbits) - 1u);
     const uint32_t tag = (a.cbits >= 32) ? 0u : ((uint32_t)(h >> 32) >> a.cbits) << a.cbits;  // high (32 - cbits) bits
     const uint32_t mine = tag | c;
-    uint32_t s = reduce32((uint32_t)h, a.m2);
+    uint32_t s = spatial ? cell_home(a.hbox + 8, k, a.m2) : reduce32((uint32_t)h, a.m2);
     for (int probe = 0; probe < kMaxProbe; ++probe) {
         uint32_t cur = __ldcg(a.table2 + s);
         if (cur == kEmpty32) {
@@ -207,6 +223,7 @@ __global__ void __launch_bounds__(kThreads, 8) k_resolve_slots(ImportArgs a, boo
     const uint32_t npairs = a.m1 >> 1;
     const uint32_t padded = (npairs + 31) & ~31u;  // whole warps stay in the loop (warp reductions below)
     const bool fast = trip_is_fast(a);
+    const bool spatial = a.cell_vpc == 1 && __ldg(a.hbox + 8) != 0;  // position-ordered homes in the value table
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < padded; p += gridDim.x * blockDim.x) {
         uint32_t mn[3] = {neutral, neutral, neutral}, mx[3] = {neutral, neutral, neutral};
         uint2 cc = make_uint2(kEmpty32, kEmpty32);
@@ -248,7 +265,7 @@ __global__ void __launch_bounds__(kThreads, 8) k_resolve_slots(ImportArgs a, boo
             } else {
 #pragma unroll
                 for (int i = 0; i < 8; ++i) k[i] = canon_bits(k[i]);
-                const uint32_t s2 = insert_value(a, c, k, tr.w, a.shape_off[tr.w], a.shape_off[tr.w + 1]);
+                const uint32_t s2 = insert_value(a, c, k, tr.w, a.shape_off[tr.w], a.shape_off[tr.w + 1], spatial);
                 if (write_aux) a.aux1[s] = s2;
                 // Speculation: no two distinct triplets share a value key (true for almost every mesh), so the
                 // first corner of every distinct triplet creates a vertex.  If a duplicate shows up anywhere,
@@ -574,6 +591,7 @@ __global__ void __launch_bounds__(kThreads, 6) k_write_vertices(ImportArgs a) {
     const uint32_t npairs = a.m1 >> 1;  // one thread per pair of slots, as in k_resolve_slots
     const bool fuse = import_is_clean(a);
     const bool fast = trip_is_fast(a);
+    const bool spatial = DETECT && a.cell_vpc == 1 && __ldg(a.hbox + 8) != 0;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t neutral = 0x80000000u;
     const uint32_t padded = DETECT ? ((npairs + 31) & ~31u) : npairs;  // whole warps for the box reduction
@@ -619,7 +637,7 @@ __global__ void __launch_bounds__(kThreads, 6) k_write_vertices(ImportArgs a) {
                     uint32_t kc[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) kc[i] = canon_bits(k[i]);
-                    insert_value(a, c, kc, tr.w, a.shape_off[tr.w], a.shape_off[tr.w + 1]);
+                    insert_value(a, c, kc, tr.w, a.shape_off[tr.w], a.shape_off[tr.w + 1], spatial);
                 }
             }
             float4 tangent = make_float4(0.f, 0.f, 0.f, 0.f);  // a vertex no triangle references keeps zeros

@@ -214,42 +214,11 @@ __global__ void __launch_bounds__(kThreads) k_flag_records(ImportArgs a) {
         const uint32_t c = __ldcs(a.sec_first + s);
         if (c < a.ncorners) atomicOr(a.fbits + (c >> 5), 1u << (c & 31));  // kEmpty32 >= ncorners
     }
-    // Box of a SAMPLE (every 8th record) of the finite position words, referenced or not: it only steers which bucket of
-    // the fingerprint table a value key starts in (store_cell_map below; positions outside it are clamped to the border
-    // cells), so it can cost locality, never correctness.
-    if (a.cell_vpc) {
-        uint32_t mn[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, mx[3] = {0u, 0u, 0u};
-        const uint32_t* pw = reinterpret_cast<const uint32_t*>(a.pos);
-        // (blocks of 256 consecutive records, every 8th block: whole sectors are used)
-        for (uint32_t r = ((tid >> 8) << 11) + (tid & 255u); r < a.np; r += (nth >> 8) << 11) {
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const uint32_t b = __ldg(pw + 3ull * r + k);
-                if (!nonfinite_bits(b)) {
-                    const uint32_t e = enc_float(__uint_as_float(canon_bits(b)));
-                    mn[k] = min(mn[k], e);
-                    mx[k] = max(mx[k], e);
-                }
-            }
-        }
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            mn[k] = __reduce_min_sync(0xFFFFFFFFu, mn[k]);
-            mx[k] = __reduce_max_sync(0xFFFFFFFFu, mx[k]);
-        }
-        if ((threadIdx.x & 31) == 0) {
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                if (mn[k] < a.hbox[k]) atomicMin(a.hbox + k, mn[k]);
-                if (mx[k] > a.hbox[3 + k]) atomicMax(a.hbox + 3 + k, mx[k]);
-            }
-        }
-    }
+    if (a.cell_vpc) sample_position_box(a, tid, nth);  // (steers the fingerprint table's bucket choice: vkm_device.cuh)
 }
 
 // vid_of[slot] = the slot's GLOBAL vertex id (its rank among all vertex-creating corners; kEmpty32 for unused slots).
 // The index pass subtracts the shape's base, which it tracks per thread anyway.
-__device__ void store_cell_map(const ImportArgs& a);
 __global__ void __launch_bounds__(kThreads) k_rank_records(ImportArgs a) {
     pdl_enter();
     if (blockIdx.x == 0 && threadIdx.x == 0) store_cell_map(a);
@@ -360,42 +329,6 @@ __global__ void __launch_bounds__(kThreads) k_write_indices_rec(ImportArgs a) {
 // scrambles.
 // The map is worked out once per import by one thread of k_rank_records (box and vertex count are final by then) and
 // parked behind the box words: hbox[8..13] = {on, axes, cells per row, min0, min1, 1 / cell size}.
-__device__ __forceinline__ float pick3(uint32_t ax, float x, float y, float z) { return ax == 0 ? x : (ax == 1 ? y : z); }
-
-__device__ void store_cell_map(const ImportArgs& a) {
-    uint32_t* o = a.hbox + 8;
-    o[0] = 0;
-    if (a.cell_vpc == 0 || a.seed != 0 || a.nshapes > 1) return;
-    float mnx, mny, mnz, ex, ey, ez;
-    {
-        const uint32_t l0 = a.hbox[0], l1 = a.hbox[1], l2 = a.hbox[2], h0 = a.hbox[3], h1 = a.hbox[4], h2 = a.hbox[5];
-        if (l0 > h0 || l1 > h1 || l2 > h2) return;  // no finite position at all
-        mnx = dec_float(l0); mny = dec_float(l1); mnz = dec_float(l2);
-        ex = __fsub_rn(dec_float(h0), mnx); ey = __fsub_rn(dec_float(h1), mny); ez = __fsub_rn(dec_float(h2), mnz);
-    }
-    // the two longest axes, longest first
-    uint32_t s0 = 0, s1 = 1;
-    if (ex >= ey && ex >= ez) { s0 = 0; s1 = ey >= ez ? 1u : 2u; }
-    else if (ey >= ex && ey >= ez) { s0 = 1; s1 = ex >= ez ? 0u : 2u; }
-    else { s0 = 2; s1 = ex >= ey ? 0u : 1u; }
-    const float e0 = pick3(s0, ex, ey, ez), e1 = pick3(s1, ex, ey, ez);
-    // as many cells as four times the buckets: four consecutive cells of a row share a bucket (cell_bucket), so the
-    // lattice covers the table once and a bucket collects about (vertices / buckets) = 4 keys of its 8 words
-    const float cells = fmaxf(4.0f * (float)(a.m2 >> 3), 1.0f);
-    const float area = __fmul_rn(e0, e1);
-    if (!(area > 0.0f) || !(area < 3.0e38f)) return;  // a line, a point, or an overflowing box
-    const float h = __fsqrt_rn(__fdiv_rn(area, cells));
-    if (!(h > 0.0f)) return;
-    const float inv_h = __fdiv_rn(1.0f, h);
-    if (!(inv_h < 3.0e38f)) return;
-    o[1] = s0 | (s1 << 2);
-    o[2] = (uint32_t)fminf(__fmul_rn(e0, inv_h), 4.0e6f) + 2u;
-    o[3] = __float_as_uint(pick3(s0, mnx, mny, mnz));
-    o[4] = __float_as_uint(pick3(s1, mnx, mny, mnz));
-    o[5] = __float_as_uint(inv_h);
-    o[0] = 1;
-}
-
 __device__ __forceinline__ uint32_t cell_bucket(const uint32_t* __restrict__ cm, const uint32_t kc[8], uint32_t nb) {
     const uint32_t axes = __ldg(cm + 1), g0 = __ldg(cm + 2);
     const float min0 = __uint_as_float(__ldg(cm + 3)), min1 = __uint_as_float(__ldg(cm + 4)), inv_h = __uint_as_float(__ldg(cm + 5));
@@ -431,10 +364,19 @@ __device__ __forceinline__ void fingerprint_start(const ImportArgs& a, bool spat
     b = (!MULTI && spatial) ? cell_bucket(a.hbox + 8, kc, nb) : reduce32((uint32_t)h, nb);
 }
 
-__device__ __forceinline__ void probe_fingerprint(const ImportArgs& a, uint32_t fp, uint32_t b, uint32_t b_lo, uint32_t nb) {
+__device__ __forceinline__ void probe_fingerprint(const ImportArgs& a, bool spatial, uint32_t fp, uint32_t b, uint32_t b_lo, uint32_t nb) {
     const int limit = (int)min(nb, 256u);
     const uint32_t rot = (b >> 30) * 2u;  // the key's own first word of every bucket (0 for hashed buckets)
     b &= 0x3FFFFFFFu;
+    // A full bucket sends the key on.  Hashed buckets: to the next one.  Position-ordered buckets: to the same column
+    // of the NEXT LATTICE ROW, not along the row -- the lattice has a few more rows than the table (margins, rounding up
+    // to whole buckets), so the last rows wrap onto the first and fill them exactly; along such a row every bucket is
+    // full and one extra key would crawl to the probe limit (67 M adversarial grid), while the row below has room.
+    uint32_t step = 1;
+    if (spatial) {
+        const uint32_t per_row = (__ldg(a.hbox + 10) + 3u) >> 2;
+        if (per_row < nb) step = per_row;
+    }
     for (int probe = 0; probe < limit; ++probe) {
         uint32_t* base = a.table2 + 8ull * (b_lo + b);
         uint32_t w[8];
@@ -466,7 +408,8 @@ __device__ __forceinline__ void probe_fingerprint(const ImportArgs& a, uint32_t 
             return;
         }
         if (done) return;
-        b = (b + 1 == nb) ? 0 : b + 1;
+        b += step;
+        if (b >= nb) b -= nb;
     }
     a.status->overflow2 = 1;
 }
@@ -576,9 +519,9 @@ __global__ void __launch_bounds__(kThreads, VKM_VTX_MINB) k_write_vertices_rec(I
 #pragma unroll
                     for (int i = 0; i < 8; ++i) kc[i] = canon_bits(k[i]);
                     fingerprint_start<MULTI>(a, spatial, kc, sh, fp, b, b_lo, nb);
-                    probe_fingerprint(a, fp, b, b_lo, nb);
+                    probe_fingerprint(a, false, fp, b, b_lo, nb);
                 } else {
-                    probe_fingerprint(a, pf_fp, pf_b, 0u, a.m2 >> 3);
+                    probe_fingerprint(a, spatial, pf_fp, pf_b, 0u, a.m2 >> 3);
                 }
 #ifndef VKM_VTX_ST128  // two 256-bit streaming stores per record (four 128-bit ones: 0.399 -> 0.387 ms the other way round)
                 {

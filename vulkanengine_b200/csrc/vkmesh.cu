@@ -527,7 +527,14 @@ int plan_enqueue(vkm_plan* p) {
     // there the launch gaps are a tenth of the import (1 M triangles: 0.121 -> 0.109 ms).  On long kernels it LOSES
     // (16 M triangles: 1.02 -> 1.07 ms): the dependent grid's CTAs move in wherever a slot frees up first, so its
     // 8-per-SM grid-stride split is no longer even and the SMs that took the extra CTAs finish late.
+    // position-ordered homes in the value table (insert_value): same conditions as the record schedule's buckets
+    a.hbox = p->hbox.p;
+    a.cell_vpc = (p->cell_on && !p->cell_off && a.nshapes == 1 && p->seed == 0 && (uint64_t)a.m2 * 4 >= (32ull << 20)) ? 1u : 0u;
     L(launch_k(false, k_clear, grid_for(std::max(a.m1, a.m2) / 4, kThreads, dev), kThreads, st, a));
+    if (a.cell_vpc) {
+        L(launch_k(Pg, k_sample_box, grid_for(a.np / 8 + 1, kThreads, dev), kThreads, st, a));
+        L(launch_k(Pg, k_cell_map, 1, 32, st, a));
+    }
     if (T) CU(cudaEventRecord(ev[PH_INSERT], st));
     {
         const unsigned g1 = grid_for(((uint64_t)a.ncorners + 3) / 4, kThreads, dev);
