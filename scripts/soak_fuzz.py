@@ -88,9 +88,14 @@ def make_dirty(rng, m):
     return synth.MeshStreams(pos, nrm, uv, idx, m.shape_offsets, dict(m.meta))
 
 
-def random_mesh(rng):
+def random_mesh(rng, big=False):
     kind = int(rng.integers(0, 4))
-    if kind == 0:
+    if big:
+        # large enough (> 3.3 M records) for the position-ordered value tables of both schedules to be in use
+        kind = 0
+        m = synth.grid(int(rng.integers(1850, 2300)), offset=tuple(float(x) for x in rng.uniform(-3, 3, 3)),
+                       scale=float(rng.uniform(0.3, 5.0)))
+    elif kind == 0:
         m = synth.grid(int(rng.integers(150, 860)))
     elif kind == 1:
         m = synth.uv_sphere(int(rng.integers(100, 700)), int(rng.integers(100, 900)))
@@ -100,7 +105,7 @@ def random_mesh(rng):
     ntri = len(idx) // 3
     so = cut_shapes(rng, ntri, int(rng.choice([1, 1, 4, 60])))
     m = synth.MeshStreams(m.pos, m.nrm, m.uv, np.ascontiguousarray(idx), so, dict(m.meta, kind=kind))
-    if rng.random() < 0.35:
+    if rng.random() < (0.5 if big else 0.35):
         m = make_dirty(rng, m)
         m.meta["dirty"] = True
     return m
@@ -110,6 +115,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--meshes", type=int, default=60)
     ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--big", action="store_true", help="4 M .. 10 M-triangle grids (position-ordered tables in use)")
     ap.add_argument("--fresh-every", type=int, default=7, help="vkm_shutdown() every N meshes: new plan, cold tables")
     args = ap.parse_args()
     assert refcpu.available(), "oracle/_ref is not built"
@@ -123,7 +129,7 @@ def main():
     with ThreadPoolExecutor(max(1, cores - 1)) as ex:
         pending = []
         for k in range(args.meshes):
-            m = random_mesh(rng)
+            m = random_mesh(rng, args.big)
             fut = ex.submit(refcpu.import_arrays, m.pos, m.nrm, m.uv, m.idx, m.shape_offsets)
             if k % args.fresh_every == 0:
                 capi.shutdown()
