@@ -32,6 +32,16 @@ sys.path.insert(0, ROOT)
 
 METRIC = "mesh triangles/sec (dedup+normals+tangents)"
 UNIT = "triangles/s"
+def general_launches(mesh, stats) -> int:
+    """Launches of one general-schedule import (vkmesh.cu plan_enqueue): 13, plus k_sample_box and k_cell_map when the
+    value table is position-ordered (single shape, table of 2 x (1.25 x records + 1024) + 64 words beyond 32 MB, hash
+    generation 0)."""
+    na = max(len(mesh.pos), len(mesh.nrm), len(mesh.uv))
+    m2 = 2 * (na + na // 4 + 1024) + 64
+    ordered = len(mesh.shape_offsets) == 2 and 4 * m2 >= (32 << 20) and int(stats.get("hash_seed", 0)) == 0
+    return 13 + (2 if ordered else 0)
+
+
 KERNELS_PER_STEP = 8  # our kernels per clean import (clear, insert, flags, scan x2, ranks, indices, vertices); vkmesh.cu plan_enqueue
 FALLBACK_HBM_GBS = 6650.0
 
@@ -623,7 +633,8 @@ def main():
             "dtype": "u32+f32", "data": "synthetic",
             "config": workload_config(args, mesh, desc, U, world), "unique_vertices_per_gpu": U,
             "roofline": roofline, "pipeline_roofline": pipeline_roofline, "schedules": schedules, "cpu_baseline": cpu_baseline, "e2e": e2e,
-            "gpu_launches": (13 if full else KERNELS_PER_STEP) * args.steps, "clocks": clocks,  # general schedule: 13 launches per import
+            "gpu_launches": (general_launches(mesh, schedules["steady_state"]["stats"]) if full else KERNELS_PER_STEP) * args.steps,
+            "clocks": clocks,
         }
         emit(line)
     if world > 1:
