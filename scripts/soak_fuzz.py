@@ -72,7 +72,7 @@ def make_dirty(rng, m):
     hit = np.isin(idx[where, 0], src)
     remap = {int(s): len(m.pos) + j for j, s in enumerate(src)}
     for w in where[hit][: 2 * k]:
-        idx[w, 0] = remap[int(idx[w, 0])]
+        idx[w, 0] = remap.get(int(idx[w, 0]), idx[w, 0])  # (a corner drawn twice is already redirected)
     # corners redirected to the copies wherever the sample did not hit: take corners that use src directly
     for j, s in enumerate(src[:50]):
         users = np.nonzero(idx[:, 0] == s)[0]
